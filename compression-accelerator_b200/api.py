@@ -1,0 +1,223 @@
+"""ctypes binding of libsnappy_b200.so (include/snappy_b200.h) and the host-side mirror of the
+reference's compress interface.
+
+Mirrors, by name and argument meaning:
+  * ``compress(source, uncompressed_length, dest) -> compressed_length`` of the RoCC driver
+    (reference tests/compression.c:20-27)                      -> :func:`rocc_compress`
+  * ``snappy::Compress(input, n, &output)`` as driven by tests/swcompression.cc:45
+                                                               -> :func:`compress`
+  * ``snappy::MaxCompressedLength`` (tests/snappy/snappy.cc:99-121) -> :func:`max_compressed_length`
+
+There is no CPU path: if the library or a CUDA device is missing these calls raise.
+torch is used only for device memory and streams (Context.*_device take torch uint8 tensors).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsnappy_b200.so")
+
+EXACT, FAST = 0, 1
+_MODES = {"exact": EXACT, "fast": FAST, EXACT: EXACT, FAST: FAST}
+OK, INVALID_INPUT, BUFFER_TOO_SMALL, CUDA_ERROR, NO_DEVICE = range(5)
+BLOCK = 65536            # tests/snappy/snappy.h:196 kBlockSize
+
+
+class SnappyB200Error(RuntimeError):
+    def __init__(self, status, text):
+        super().__init__("libsnappy_b200 status %d: %s" % (status, text))
+        self.status = status
+
+
+_lib = None
+
+# name -> (restype, argtypes); every symbol include/snappy_b200.h declares
+SYMBOLS = {
+    "snappy_b200_max_compressed_length": (C.c_size_t, [C.c_size_t]),
+    "snappy_b200_last_error": (C.c_char_p, []),
+    "snappy_b200_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
+    "snappy_b200_destroy": (None, [C.c_void_p]),
+    "snappy_b200_stream": (C.c_void_p, [C.c_void_p]),
+    "snappy_b200_compress": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                       C.POINTER(C.c_size_t), C.c_int]),
+    "snappy_b200_compress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                              C.c_size_t, C.c_void_p, C.c_int]),
+    "snappy_b200_compress_fragments_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t,
+                                                        C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]),
+    "snappy_b200_compress_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
+                                                    C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p,
+                                                    C.c_int]),
+    "snappy_b200_compress_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
+                                             C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]),
+    "snappy_b200_varint32": (C.c_size_t, [C.c_void_p, C.c_uint32]),
+    "snappy_b200_sync": (C.c_int, [C.c_void_p]),
+    "snappy_b200_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "snappy_b200_host_free": (None, [C.c_void_p]),
+    "snappy_b200_launch_count": (C.c_ulonglong, [C.c_void_p]),
+    "snappy_b200_last_kernel_ms": (C.c_float, [C.c_void_p]),
+    "snappy_b200_rocc_compress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
+    "snappy_b200_rocc_uncompress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
+}
+
+
+def lib():
+    """Load libsnappy_b200.so (fails loudly if it was not built: run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SnappyB200Error(NO_DEVICE, "%s not built (python -c 'import __graft_entry__ as g; "
+                                  "g.build()')" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _check(status):
+    if status != OK:
+        raise SnappyB200Error(status, lib().snappy_b200_last_error().decode())
+
+
+def max_compressed_length(n: int) -> int:
+    return lib().snappy_b200_max_compressed_length(n)
+
+
+def varint32(n: int) -> bytes:
+    buf = C.create_string_buffer(8)
+    k = lib().snappy_b200_varint32(buf, n)
+    return buf.raw[:k]
+
+
+def _addr(buf):
+    """Address of a bytes / bytearray / numpy array / ctypes buffer without copying."""
+    if isinstance(buf, (bytes, bytearray)):
+        return C.cast(C.c_char_p(bytes(buf)) if isinstance(buf, bytearray) else C.c_char_p(buf), C.c_void_p).value
+    if hasattr(buf, "ctypes"):
+        return buf.ctypes.data
+    if hasattr(buf, "data_ptr"):
+        return buf.data_ptr()
+    return C.addressof(buf)
+
+
+class Context:
+    """One CUDA stream plus device scratch (snappy_b200_ctx).  Not thread-safe; make one per
+    host thread, as one RoCC unit serves one command at a time (CompressionAccelerator.scala:72)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        _check(lib().snappy_b200_create(C.byref(h), device))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().snappy_b200_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def stream(self) -> int:
+        return lib().snappy_b200_stream(self._h) or 0
+
+    @property
+    def launches(self) -> int:
+        return lib().snappy_b200_launch_count(self._h)
+
+    @property
+    def last_kernel_ms(self) -> float:
+        return lib().snappy_b200_last_kernel_ms(self._h)
+
+    def sync(self):
+        _check(lib().snappy_b200_sync(self._h))
+
+    # ---- host buffers -------------------------------------------------------------------
+    def compress(self, data, mode="exact") -> bytes:
+        """snappy::Compress(input, n, &output) (tests/swcompression.cc:45): host bytes in, the
+        compressed stream out."""
+        n = len(data)
+        cap = max_compressed_length(n)
+        out = C.create_string_buffer(cap + 16)
+        out_n = C.c_size_t(0)
+        src = data if isinstance(data, bytes) else bytes(data)
+        _check(lib().snappy_b200_compress(self._h, src, n, out, cap, C.byref(out_n), _MODES[mode]))
+        return out.raw[:out_n.value]
+
+    def compress_into(self, src_addr: int, n: int, dst_addr: int, dst_cap: int, mode="exact") -> int:
+        """Raw-pointer flavour (pinned or pageable host memory); returns the stream length."""
+        out_n = C.c_size_t(0)
+        _check(lib().snappy_b200_compress(self._h, src_addr, n, dst_addr, dst_cap, C.byref(out_n),
+                                          _MODES[mode]))
+        return out_n.value
+
+    def compress_batch(self, buf, length: int, stride: int, count: int, mode="exact"):
+        """`count` buffers of `length` bytes at `stride` -> (out uint8 array, out_stride, sizes);
+        each buffer is its own Snappy stream (RawCompress per buffer, snappy.cc:1404-1414)."""
+        import numpy as np
+        arr = np.frombuffer(buf, dtype=np.uint8) if not hasattr(buf, "ctypes") else buf
+        ostride = max_compressed_length(length)
+        out = np.zeros(ostride * count + 16, dtype=np.uint8)
+        sizes = np.zeros(count, dtype=np.uint32)
+        _check(lib().snappy_b200_compress_batch(self._h, arr.ctypes.data, length, stride, count,
+                                                out.ctypes.data, ostride, sizes.ctypes.data, _MODES[mode]))
+        return out, ostride, sizes
+
+    # ---- device tensors (torch uint8, on this context's device) -------------------------
+    def compress_device(self, src, dst=None, out_n=None, mode="exact", header=True):
+        """Compress a device-resident stream.  Returns (dst, out_n): dst a uint8 device tensor of
+        capacity max_compressed_length(n), out_n a 1-element int64 device tensor with the
+        stream length.  Asynchronous on self.stream.  header=False compresses a run of whole
+        fragments without the varint preamble (multi-GPU shards)."""
+        import torch
+        n = src.numel()
+        cap = max_compressed_length(n)
+        if dst is None:
+            dst = torch.empty(cap, dtype=torch.uint8, device=src.device)
+        if out_n is None:
+            out_n = torch.zeros(1, dtype=torch.int64, device=src.device)
+        fn = lib().snappy_b200_compress_device if header else lib().snappy_b200_compress_fragments_device
+        _check(fn(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(), out_n.data_ptr(), _MODES[mode]))
+        return dst, out_n
+
+    def compress_batch_device(self, src, length, stride, count, dst=None, sizes=None, mode="exact"):
+        import torch
+        ostride = max_compressed_length(length)
+        if dst is None:
+            dst = torch.empty(ostride * count, dtype=torch.uint8, device=src.device)
+        if sizes is None:
+            sizes = torch.zeros(count, dtype=torch.int32, device=src.device)
+        _check(lib().snappy_b200_compress_batch_device(self._h, src.data_ptr(), length, stride, count,
+                                                       dst.data_ptr(), ostride, sizes.data_ptr(),
+                                                       _MODES[mode]))
+        return dst, ostride, sizes
+
+
+_default = None
+
+
+def default_context() -> Context:
+    global _default
+    if _default is None:
+        _default = Context(0)
+    return _default
+
+
+def compress(data, mode="exact") -> bytes:
+    """snappy::Compress on the default context (device 0)."""
+    return default_context().compress(data, mode)
+
+
+def rocc_compress(source, uncompressed_length: int, dest) -> int:
+    """compress(source, uncompressed_length, dest) of tests/compression.c:20-27: writes the stream
+    into the caller-sized `dest` (a writable ctypes / numpy buffer) and returns its length
+    (0 on failure)."""
+    src = source if isinstance(source, bytes) else _addr(source)
+    return int(lib().snappy_b200_rocc_compress(src, uncompressed_length, _addr(dest)))
+
+
+def rocc_uncompress(source, compressed_length: int, dest) -> int:
+    """uncompress(source, compressed_length, dest) of tests/compression.c:32-39: 0 on success."""
+    src = source if isinstance(source, bytes) else _addr(source)
+    return int(lib().snappy_b200_rocc_uncompress(src, compressed_length, _addr(dest)))

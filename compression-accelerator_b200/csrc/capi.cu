@@ -1,0 +1,298 @@
+// capi.cu -- the C-ABI of libsnappy_b200 (include/snappy_b200.h): contexts, scratch, the
+// stream / fragment-range / batch entry points and the RoCC driver mirror.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+
+#include "../../include/snappy_b200.h"
+#include "kernels.h"
+#include "snappy_device.cuh"
+
+namespace {
+
+thread_local char g_err[256] = "";
+
+snappy_b200_status fail(snappy_b200_status st, const char* what, cudaError_t e = cudaSuccess) {
+    if (e != cudaSuccess)
+        snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
+    else
+        snprintf(g_err, sizeof g_err, "%s", what);
+    return st;
+}
+
+#define CU(call)                                                                  \
+    do {                                                                          \
+        cudaError_t e_ = (call);                                                  \
+        if (e_ != cudaSuccess) return fail(SNAPPY_B200_CUDA_ERROR, #call, e_);    \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct snappy_b200_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    DevBuf staging, sizes, offsets, d_in, d_out;
+    unsigned long long* d_total = nullptr;     // device
+    unsigned long long* h_total = nullptr;     // pinned
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    unsigned long long launches = 0;
+    float last_ms = 0.f;
+};
+
+namespace {
+
+std::once_flag g_init_once;
+cudaError_t g_init_err = cudaSuccess;
+
+snappy_b200_status bind(snappy_b200_ctx* c) {
+    CU(cudaSetDevice(c->device));
+    return SNAPPY_B200_OK;
+}
+
+thread_local snappy_b200_ctx* g_default_ctx = nullptr;
+
+snappy_b200_status default_ctx(snappy_b200_ctx** out) {
+    if (!g_default_ctx) {
+        snappy_b200_status st = snappy_b200_create(&g_default_ctx, 0);
+        if (st != SNAPPY_B200_OK) return st;
+    }
+    *out = g_default_ctx;
+    return SNAPPY_B200_OK;
+}
+
+// Stream / fragment-range compression with input and output on the device.
+snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst,
+                                size_t dst_cap, unsigned long long* d_out_n, int mode,
+                                bool with_header) {
+    if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
+    if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST)
+        return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
+    if (dst_cap < snappy_b200_max_compressed_length(n) - (with_header ? 0 : 0))
+        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
+    const uint32_t hdr = with_header ? sb::varint32_len((uint32_t)n) : 0;
+    CU(c->staging.reserve((size_t)n_frag * sb::kStageStride + 256));
+    CU(c->sizes.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
+    CU(c->offsets.reserve((size_t)(n_frag + 1) * sizeof(unsigned long long)));
+    sb::ParseParams p;
+    p.in = (const uint8_t*)d_src;
+    p.n_total = n;
+    p.in_stride = sb::kBlock;
+    p.job_len = sb::kBlock;
+    p.out = (uint8_t*)c->staging.p;
+    p.out_stride = sb::kStageStride;
+    p.sizes = (uint32_t*)c->sizes.p;
+    p.n_jobs = n_frag;
+    p.with_header = 0;
+    CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    CU(sb::launch_scan((const uint32_t*)c->sizes.p, n_frag, (unsigned long long*)c->offsets.p, hdr,
+                       (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
+    CU(sb::launch_compact((const uint8_t*)c->staging.p, sb::kStageStride, (const uint32_t*)c->sizes.p,
+                          (const unsigned long long*)c->offsets.p, n_frag, (uint8_t*)d_dst,
+                          c->stream, &c->launches));
+    return SNAPPY_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t snappy_b200_max_compressed_length(size_t n) { return 32 + n + n / 6; }
+
+const char* snappy_b200_last_error(void) { return g_err; }
+
+size_t snappy_b200_varint32(void* dst, uint32_t n) { return sb::put_varint32((uint8_t*)dst, n); }
+
+snappy_b200_status snappy_b200_create(snappy_b200_ctx** out, int device) {
+    if (!out) return fail(SNAPPY_B200_INVALID_INPUT, "null ctx pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(SNAPPY_B200_NO_DEVICE, "no CUDA device (libsnappy_b200 has no CPU path)", e);
+    if (device < 0 || device >= count) return fail(SNAPPY_B200_INVALID_INPUT, "bad device ordinal");
+    CU(cudaSetDevice(device));
+    std::call_once(g_init_once, [] { g_init_err = sb::kernels_init(); });
+    if (g_init_err != cudaSuccess) return fail(SNAPPY_B200_CUDA_ERROR, "kernels_init", g_init_err);
+    snappy_b200_ctx* c = new (std::nothrow) snappy_b200_ctx;
+    if (!c) return fail(SNAPPY_B200_CUDA_ERROR, "out of host memory");
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaMalloc(&c->d_total, sizeof(unsigned long long)));
+    CU(cudaMallocHost(&c->h_total, sizeof(unsigned long long)));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    *out = c;
+    return SNAPPY_B200_OK;
+}
+
+void snappy_b200_destroy(snappy_b200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->staging.release(); c->sizes.release(); c->offsets.release();
+    c->d_in.release(); c->d_out.release();
+    if (c->d_total) cudaFree(c->d_total);
+    if (c->h_total) cudaFreeHost(c->h_total);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (g_default_ctx == c) g_default_ctx = nullptr;
+    delete c;
+}
+
+void* snappy_b200_stream(snappy_b200_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+unsigned long long snappy_b200_launch_count(snappy_b200_ctx* c) { return c ? c->launches : 0; }
+
+float snappy_b200_last_kernel_ms(snappy_b200_ctx* c) { return c ? c->last_ms : 0.f; }
+
+snappy_b200_status snappy_b200_sync(snappy_b200_ctx* c) {
+    if (!c) return fail(SNAPPY_B200_INVALID_INPUT, "null ctx");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(cudaStreamSynchronize(c->stream));
+    return SNAPPY_B200_OK;
+}
+
+void* snappy_b200_host_alloc(size_t n) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, n ? n : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+
+void snappy_b200_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+snappy_b200_status snappy_b200_compress_device(snappy_b200_ctx* c, const void* d_src, size_t n,
+                                               void* d_dst, size_t dst_cap,
+                                               unsigned long long* d_out_n, int mode) {
+    if (!c || !d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, true);
+}
+
+snappy_b200_status snappy_b200_compress_fragments_device(snappy_b200_ctx* c, const void* d_src,
+                                                         size_t n, void* d_dst, size_t dst_cap,
+                                                         unsigned long long* d_out_n, int mode) {
+    if (!c || !d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, false);
+}
+
+snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const void* d_src,
+                                                     size_t len, size_t in_stride, size_t count,
+                                                     void* d_dst, size_t out_stride,
+                                                     uint32_t* d_sizes, int mode) {
+    if (!c || !d_dst || !d_sizes || (!d_src && len && count))
+        return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (len > sb::kBlock) return fail(SNAPPY_B200_INVALID_INPUT, "batch buffers are limited to 65536 bytes");
+    if (count > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "too many buffers");
+    if (in_stride < len) return fail(SNAPPY_B200_INVALID_INPUT, "in_stride < len");
+    if (out_stride < snappy_b200_max_compressed_length(len))
+        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "out_stride < max_compressed_length(len)");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    if (count == 0) return SNAPPY_B200_OK;
+    sb::ParseParams p;
+    p.in = (const uint8_t*)d_src;
+    p.n_total = (count - 1) * in_stride + len;
+    p.in_stride = in_stride;
+    p.job_len = (uint32_t)len;
+    p.out = (uint8_t*)d_dst;
+    p.out_stride = out_stride;
+    p.sizes = d_sizes;
+    p.n_jobs = (uint32_t)count;
+    p.with_header = 1;
+    CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_compress(snappy_b200_ctx* c, const void* src, size_t n, void* dst,
+                                        size_t dst_cap, size_t* out_n, int mode) {
+    if (!dst || !out_n || (!src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
+    if (dst_cap < snappy_b200_max_compressed_length(n))
+        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");
+    if (!c) { snappy_b200_status st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    const size_t cap = snappy_b200_max_compressed_length(n);
+    CU(c->d_in.reserve(n + 64));
+    CU(c->d_out.reserve(cap + 64));
+    if (n) CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    snappy_b200_status st = compress_dev(c, c->d_in.p, n, c->d_out.p, cap, c->d_total, mode, true);
+    if (st != SNAPPY_B200_OK) return st;
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const size_t total = (size_t)*c->h_total;
+    if (total > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "stream larger than dst_cap");
+    CU(cudaMemcpyAsync(dst, c->d_out.p, total, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    *out_n = total;
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_compress_batch(snappy_b200_ctx* c, const void* src, size_t len,
+                                              size_t in_stride, size_t count, void* dst,
+                                              size_t out_stride, uint32_t* sizes, int mode) {
+    if (!dst || !sizes || (!src && len && count)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (!c) { snappy_b200_status st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    if (count == 0) return SNAPPY_B200_OK;
+    if (in_stride < len) return fail(SNAPPY_B200_INVALID_INPUT, "in_stride < len");
+    const size_t in_bytes = (count - 1) * in_stride + len, out_bytes = count * out_stride;
+    CU(c->d_in.reserve(in_bytes + 64));
+    CU(c->d_out.reserve(out_bytes + 64));
+    CU(c->sizes.reserve((count + 1) * sizeof(uint32_t)));
+    CU(cudaMemcpyAsync(c->d_in.p, src, in_bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    snappy_b200_status st = snappy_b200_compress_batch_device(c, c->d_in.p, len, in_stride, count, c->d_out.p,
+                                                              out_stride, (uint32_t*)c->sizes.p, mode);
+    if (st != SNAPPY_B200_OK) return st;
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(sizes, c->sizes.p, count * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(dst, c->d_out.p, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    return SNAPPY_B200_OK;
+}
+
+/* tests/compression.c:20-27: compress(source, uncompressed_length, dest) -> compressed length.
+ * The caller sizes dest (no capacity argument in the reference contract). */
+unsigned long snappy_b200_rocc_compress(char* source, int uncompressed_length, char* dest) {
+    if (uncompressed_length < 0) { fail(SNAPPY_B200_INVALID_INPUT, "negative length"); return 0; }
+    size_t out_n = 0;
+    size_t n = (size_t)uncompressed_length;
+    snappy_b200_status st = snappy_b200_compress(nullptr, source, n, dest,
+                                                 snappy_b200_max_compressed_length(n), &out_n,
+                                                 SNAPPY_B200_EXACT);
+    return st == SNAPPY_B200_OK ? (unsigned long)out_n : 0ul;
+}
+
+/* tests/compression.c:32-39.  The reference hardware never implemented this command
+ * (CompressionAccelerator.scala:385-388 only raises busy); until the device decompressor of
+ * SURVEY.md section 8f lands it reports failure (non-zero), as the contract allows. */
+unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, char* dest) {
+    (void)source; (void)compressed_length; (void)dest;
+    fail(SNAPPY_B200_INVALID_INPUT, "uncompress: device decompressor not built yet");
+    return 1ul;
+}
+
+}  // extern "C"

@@ -1,0 +1,115 @@
+/*
+ * snappy_b200.h -- C-ABI of libsnappy_b200: a B200 (sm_100a) Snappy block compressor that
+ * stands in for the RoCC compression accelerator of nullromo/compression-accelerator.
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * reference repository).  Plain pointers and sizes only; no torch / C++ types.
+ *
+ * Streams produced are standard Snappy raw streams (tests/snappy/format_description.txt):
+ * varint32(uncompressed length) followed by the elements of independent <=64 KiB fragments.
+ * In SNAPPY_B200_EXACT mode the bytes are identical to the reference's software Snappy
+ * (tests/snappy/snappy.cc:1002-1070 as driven by tests/swcompression.cc:45).
+ */
+#ifndef SNAPPY_B200_H_
+#define SNAPPY_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Status codes: first three mirror tests/snappy/snappy-c.h:46-50 (snappy_status). */
+typedef enum {
+    SNAPPY_B200_OK = 0,
+    SNAPPY_B200_INVALID_INPUT = 1,
+    SNAPPY_B200_BUFFER_TOO_SMALL = 2,
+    SNAPPY_B200_CUDA_ERROR = 3,
+    SNAPPY_B200_NO_DEVICE = 4
+} snappy_b200_status;
+
+/* Parse mode.  EXACT keeps Snappy's greedy sequential parse and skip heuristic per fragment
+ * (tests/snappy/snappy.cc:539-671) and is byte-identical to the reference.  FAST is a
+ * parallel parse: always a valid Snappy stream, bytes may differ. */
+typedef enum { SNAPPY_B200_EXACT = 0, SNAPPY_B200_FAST = 1 } snappy_b200_mode;
+
+typedef struct snappy_b200_ctx snappy_b200_ctx; /* owns one CUDA stream + device/pinned scratch */
+
+/* tests/snappy/snappy.cc:99-121 MaxCompressedLength / snappy-c.h:107 = 32 + n + n/6 */
+size_t snappy_b200_max_compressed_length(size_t n);
+
+/* Human-readable text of the last failure on the calling thread ("" if none). */
+const char* snappy_b200_last_error(void);
+
+/* Context lifetime.  device = CUDA ordinal.  One context may be used by one host thread at a
+ * time; independent contexts are independent (the RoCC unit accepts one command at a time,
+ * CompressionAccelerator.scala:72; software Snappy is re-entrant, snappy.cc:1011). */
+snappy_b200_status snappy_b200_create(snappy_b200_ctx** ctx, int device);
+void snappy_b200_destroy(snappy_b200_ctx* ctx);
+/* The cudaStream_t the context launches on (as void*), for callers that order work around it. */
+void* snappy_b200_stream(snappy_b200_ctx* ctx);
+
+/* ---- host-pointer entry: replaces snappy::Compress / RawCompress (snappy.cc:1404-1425) and
+ * the RoCC compress command (tests/compression.c:20-27).  Synchronous: H2D, kernels, D2H.
+ * ctx may be NULL (a per-thread default context on device 0 is used).  n must be < 2^32
+ * (Snappy's header is a varint32, snappy.cc:1006-1007). */
+snappy_b200_status snappy_b200_compress(snappy_b200_ctx* ctx, const void* src, size_t n,
+                                        void* dst, size_t dst_cap, size_t* out_n, int mode);
+
+/* ---- device-pointer entry: same stream, input and output already in HBM.  Asynchronous on
+ * the context's stream; *d_out_n (device uint64) receives the stream length.  dst_cap must be
+ * >= snappy_b200_max_compressed_length(n). */
+snappy_b200_status snappy_b200_compress_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
+                                               void* d_dst, size_t dst_cap,
+                                               unsigned long long* d_out_n, int mode);
+
+/* ---- fragment-range entry (multi-GPU building block): compress n bytes that are a run of
+ * whole 64 KiB fragments of a larger stream (only the last rank's run may end short) WITHOUT
+ * the varint header; the payload lands contiguous at d_dst, its size in *d_out_n.  Rank r's
+ * payload is placed at header_len + sum of earlier ranks' sizes (snappy.cc:1013-1061). */
+snappy_b200_status snappy_b200_compress_fragments_device(snappy_b200_ctx* ctx, const void* d_src,
+                                                         size_t n, void* d_dst, size_t dst_cap,
+                                                         unsigned long long* d_out_n, int mode);
+
+/* ---- batch entry: `count` independent buffers of `len` bytes (len <= 65536) at
+ * d_src + i*in_stride, each compressed into ITS OWN Snappy stream at d_dst + i*out_stride
+ * (out_stride >= max_compressed_length(len)); d_sizes[i] (device uint32) = stream length.
+ * Equivalent to calling RawCompress once per buffer (snappy.cc:1404-1414); the page-shaped
+ * workload of benchmark/hw_results.csv.  Asynchronous on the context's stream. */
+snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* ctx, const void* d_src,
+                                                     size_t len, size_t in_stride, size_t count,
+                                                     void* d_dst, size_t out_stride,
+                                                     uint32_t* d_sizes, int mode);
+/* Host-pointer flavour of the batch entry (synchronous). */
+snappy_b200_status snappy_b200_compress_batch(snappy_b200_ctx* ctx, const void* src, size_t len,
+                                              size_t in_stride, size_t count, void* dst,
+                                              size_t out_stride, uint32_t* sizes, int mode);
+
+/* Write varint32(n) at dst (host memory), return its length 1..5
+ * (tests/snappy/snappy-stubs-internal.h:552-578). */
+size_t snappy_b200_varint32(void* dst, uint32_t n);
+
+/* Block until everything queued on the context's stream is done. */
+snappy_b200_status snappy_b200_sync(snappy_b200_ctx* ctx);
+
+/* Pinned host memory helpers (so callers can hand the host entry DMA-able buffers). */
+void* snappy_b200_host_alloc(size_t n);
+void snappy_b200_host_free(void* p);
+
+/* Kernel launch counters of the context (for bench.py's gpu_launches claim). */
+unsigned long long snappy_b200_launch_count(snappy_b200_ctx* ctx);
+
+/* Device time in ms of the last host-entry call's kernels (CUDA events), 0 if none. */
+float snappy_b200_last_kernel_ms(snappy_b200_ctx* ctx);
+
+/* ---- RoCC driver mirror: tests/compression.c:20-27 and :32-39.  Host pointers, blocking.
+ * compress returns the compressed length (0 on failure: a valid stream is never empty);
+ * uncompress returns 0 on success, non-zero on failure, as the reference documents. */
+unsigned long snappy_b200_rocc_compress(char* source, int uncompressed_length, char* dest);
+unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, char* dest);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SNAPPY_B200_H_ */

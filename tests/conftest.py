@@ -19,3 +19,20 @@ def oracle():
     """Strongest CPU checker available (compiled reference if present, else the port)."""
     import oracle_lib
     return oracle_lib.checker()
+
+
+@pytest.fixture(scope="session")
+def pkg():
+    """The product package (compression-accelerator_b200/), loaded by path."""
+    import __graft_entry__ as g
+    if not os.path.exists(os.path.join(g.PKG_DIR, "libsnappy_b200.so")):
+        g.build()
+    return g.load_package()
+
+
+@pytest.fixture(scope="session")
+def ctx(pkg):
+    """A device context on cuda:0; GPU tests only."""
+    c = pkg.Context(0)
+    yield c
+    c.close()

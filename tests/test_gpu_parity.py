@@ -1,0 +1,147 @@
+"""GPU parity tests proper: the CUDA path, called through the C-ABI, against the CPU oracle
+(bit-exact: this is byte/integer work) and against the committed golden vectors."""
+import ctypes as C
+import hashlib
+
+import numpy as np
+import pytest
+
+import corpus
+
+pytestmark = pytest.mark.gpu
+MAN = corpus.manifest()
+
+
+def roundtrip(oracle, comp: bytes, data: bytes):
+    assert oracle.uncompress(comp, len(data)) == data
+
+
+@pytest.mark.parametrize("name", sorted(MAN["files"]))
+def test_golden_files_exact(ctx, oracle, name):
+    """Every reference data file: GPU stream == golden sha256 (made by the reference's Snappy)."""
+    data = corpus.fixture(name)
+    ent = MAN["files"][name]
+    comp = ctx.compress(data)
+    assert len(comp) == ent["compressed_n"]
+    assert hashlib.sha256(comp).hexdigest() == ent["sha256"]
+    roundtrip(oracle, comp, data)
+
+
+@pytest.mark.parametrize("name", sorted(MAN["kats"]))
+def test_kats_exact(ctx, name):
+    ent = MAN["kats"][name]
+    data = bytes.fromhex(ent["input_hex"]) if "input_hex" in ent else {
+        "a4096": b"a" * 4096, "a65536": b"a" * 65536, "a70000": b"a" * 70000,
+        "ab_period3_300": b"abc" * 100}[name]
+    comp = ctx.compress(data)
+    assert len(comp) == ent["compressed_n"]
+    if "hex" in ent:
+        assert comp.hex() == ent["hex"]
+
+
+def test_thistle_through_rocc_driver_contract(pkg, oracle):
+    """tests/compression.c:41-50: 130-byte string into a caller-sized 256-byte array."""
+    dest = C.create_string_buffer(256)
+    n = pkg.rocc_compress(corpus.THISTLE, 130, dest)
+    assert n == 112
+    assert dest.raw[:n] == oracle.compress(corpus.THISTLE)
+
+
+@pytest.mark.parametrize("kind", ["random", "real", "repeating"])
+def test_benchmark_sweep_exact(ctx, oracle, kind):
+    """benchmark/benchmark-data size sweep (DataGenerator.scala:27): lengths as sw_results.csv."""
+    for n in corpus.SWEEP_SIZES:
+        data = corpus.benchmark_file(kind, n)
+        comp = ctx.compress(data)
+        assert comp == oracle.compress(data), (kind, n)
+        assert len(comp) == MAN["sweep"]["%s-%d" % (kind, n)]["compressed_n"]
+
+
+def test_all_small_lengths(ctx, oracle):
+    rng = np.random.default_rng(7)
+    base = bytes(rng.integers(97, 101, size=300, dtype=np.uint8))
+    for n in list(range(0, 80)) + [255, 256, 257, 299]:
+        assert ctx.compress(base[:n]) == oracle.compress(base[:n]), n
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_structured_random_exact(ctx, oracle, seed):
+    n = [1, 14, 15, 16, 100, 4096, 65535, 65536, 65537, 70000, 200000, 300001][seed]
+    data = corpus.structured_random(n, seed)
+    comp = ctx.compress(data)
+    assert comp == oracle.compress(data)
+    roundtrip(oracle, comp, data)
+
+
+def test_unaligned_device_source(ctx, oracle):
+    """Source not 16-byte aligned: the TMA path must fall back to ordinary loads."""
+    import torch
+    data = corpus.fixture("alice29.txt")
+    buf = torch.zeros(len(data) + 64, dtype=torch.uint8, device="cuda")
+    for shift in (1, 3, 8, 17):
+        src = buf[shift:shift + len(data)]
+        src.copy_(torch.frombuffer(bytearray(data), dtype=torch.uint8))
+        torch.cuda.synchronize()
+        dst, out_n = ctx.compress_device(src)
+        ctx.sync()
+        n = int(out_n.item())
+        assert bytes(dst[:n].cpu().numpy()) == oracle.compress(data), shift
+
+
+def test_batch_pages_exact(ctx, oracle):
+    """Config 4 shape: independent 4 KiB buffers, each its own stream (header 80 20)."""
+    text = corpus.fixture("all-mtg-cards.txt")
+    count = 512
+    pages = bytearray(text[:4096 * (count - 64)])
+    pages += bytes(corpus.random_ascii(4096 * 32, 1)) + b"a" * (4096 * 32)
+    out, ostride, sizes = ctx.compress_batch(np.frombuffer(bytes(pages), dtype=np.uint8), 4096, 4096, count)
+    ref_out, ref_stride, ref_sizes = oracle.compress_batch(bytes(pages), 4096, 4096, count)
+    assert ostride == ref_stride and (sizes == ref_sizes).all()
+    for i in range(count):
+        assert bytes(out[i * ostride:i * ostride + sizes[i]]) == bytes(ref_out[i * ostride:i * ostride + sizes[i]]), i
+        assert bytes(out[i * ostride:i * ostride + 2]) == b"\x80\x20"
+
+
+@pytest.mark.parametrize("length", [1, 14, 15, 100, 255, 256, 1000, 5000, 16384, 50000, 65536])
+def test_batch_size_sweep(ctx, oracle, length):
+    text = corpus.fixture("alice29.txt")
+    count = 16
+    stride = length + 3          # ragged stride: sources are not 16-byte aligned
+    buf = np.frombuffer((text * 8)[:stride * count], dtype=np.uint8).copy()
+    out, ostride, sizes = ctx.compress_batch(buf, length, stride, count)
+    for i in range(count):
+        want = oracle.compress(bytes(buf[i * stride:i * stride + length]))
+        assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
+
+
+def test_fragment_range_entry(ctx, oracle):
+    """Multi-GPU building block: payload of a run of whole fragments, no header."""
+    import torch
+    data = corpus.fixture("all-mtg-cards.txt")[:65536 * 5 + 1234]
+    full = oracle.compress(data)
+    hdr = 3
+    parts = []
+    for lo, hi in ((0, 65536 * 2), (65536 * 2, 65536 * 5), (65536 * 5, len(data))):
+        src = torch.frombuffer(bytearray(data[lo:hi]), dtype=torch.uint8).cuda()
+        dst, out_n = ctx.compress_device(src, header=False)
+        ctx.sync()
+        parts.append(bytes(dst[:int(out_n.item())].cpu().numpy()))
+    assert full[:hdr] + b"".join(parts) == full
+
+
+def test_large_stream_property(ctx, oracle):
+    """256 MiB of concatenated MTG text: sampled fragments equal the oracle's, sizes add up."""
+    import torch
+    n = 256 << 20
+    host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)
+    src = torch.from_numpy(host).cuda()
+    dst, out_n = ctx.compress_device(src)
+    ctx.sync()
+    total = int(out_n.item())
+    comp = dst[:total].cpu().numpy()
+    assert bytes(comp[:5]) == bytes([0x80, 0x80, 0x80, 0x80, 0x01])
+    # full decode through the CPU decompressor restores the input (round trip at full size)
+    assert oracle.uncompress(bytes(comp), n) == host.tobytes()
+    # first 4 MiB compared bytewise with the oracle's stream of the same prefix fragments
+    pre = oracle.compress(host[:4 << 20].tobytes())
+    assert bytes(comp[5:5 + len(pre) - 4]) == pre[4:]
