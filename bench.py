@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py -- Snappy-compress input GB/s on B200 (BASELINE.json metric), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode exact|fast]
+
+A "step" is one pass of the hot path over one batch: at N=1 the batch is ONE Snappy stream of
+1 GiB of compressible text (reference data/all-mtg-cards.txt concatenated, SURVEY.md section 8d
+config 2 -- the configuration BASELINE.json's target is quoted on), exact mode.  Under torchrun
+(N>1) every rank holds 1 GiB of the corpus (weak scaling); the step compresses each rank's
+fragments, all-gathers the compressed sizes over NCCL, scans them into archive offsets and
+gathers the payload on rank 0.
+
+value   = input bytes of all ranks / max-over-ranks device time, inputs resident in HBM.
+e2e     = the same metric through the host-pointer C-ABI entry (snappy_b200_compress) with
+          pinned HOST buffers: H2D of the input and D2H of the stream inside the timed region.
+roofline= the parse kernel's algorithmic bytes (N_in + N_out) / its CUDA-event duration,
+          against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
+cpu_baseline = the reference's own Snappy (oracle/_ref, compiled from /root/reference) timed on
+          this box's host cores on a bounded sample of the same workload.
+`--impl reference` times that CPU implementation as the arm itself.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+GIB = 1 << 30
+WORKLOAD = "all-mtg-cards.txt concatenated to 1 GiB, one Snappy stream per GPU"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def corpus_1gib():
+    import corpus
+    return corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), GIB)
+
+
+def cpu_reference(host, threads, budget_s=12.0):
+    """Time the reference's Snappy on `threads` host threads over a bounded sample of `host`."""
+    import oracle_lib
+    lib = oracle_lib.checker()
+    kind = "reference" if isinstance(lib, oracle_lib.Ref) else "port"
+    # size the sample from a short probe so the run takes about budget_s
+    probe = host[: 8 << 20]
+    s, _ = lib.bench(probe, 65536, 1, 1)
+    rate1 = probe.size / s
+    sample = int(min(host.size, max(64 << 20, rate1 * threads * budget_s * 0.5)))
+    sample -= sample % 65536
+    arr = host[:sample]
+    secs, produced = lib.bench(arr, 1 << 20, threads, 1)
+    return {"value": sample / secs / 1e9, "unit": "GB/s", "cores": threads, "kind": kind,
+            "sample": "first %d MiB of the workload, %d thread(s), 1 MiB slices of whole 64 KiB fragments, 1 pass"
+                      % (sample >> 20, threads), "ratio_out_in": produced / sample}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    host = corpus_1gib()
+    threads = os.cpu_count() or 1
+    import oracle_lib
+    lib = oracle_lib.checker()
+    kind = "reference" if isinstance(lib, oracle_lib.Ref) else "port"
+    probe = host[: 8 << 20]
+    s, _ = lib.bench(probe, 65536, 1, 1)
+    sample = int(min(host.size, max(64 << 20, probe.size / s * threads * 4.0)))
+    sample -= sample % 65536
+    arr = host[:sample]
+    for _ in range(args.warmup):
+        lib.bench(arr, 1 << 20, threads, 1)
+    t = 0.0
+    for _ in range(args.steps):
+        secs, produced = lib.bench(arr, 1 << 20, threads, 1)
+        t += secs
+    val = sample * args.steps / t / 1e9
+    line = {"impl": "reference", "metric": "snappy_compress_input_GBps", "value": val, "unit": "GB/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "mode": "exact"},
+            "cpu_baseline": {"value": val, "unit": "GB/s", "cores": threads, "kind": kind,
+                             "sample": "each step = first %d MiB of the workload on %d host threads" % (sample >> 20, threads)},
+            "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log("note: WORLD_SIZE=%d, --gpus=%d; using WORLD_SIZE" % (world, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pkg = g.load_package()
+    ctx = pkg.Context(local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+    host = corpus_1gib()
+    n = host.size
+    pinned_in = torch.empty(n, dtype=torch.uint8).pin_memory()
+    pinned_in.numpy()[:] = host
+    src = torch.empty(n, dtype=torch.uint8, device=dev)
+    src.copy_(pinned_in, non_blocking=True)
+    cap = pkg.max_compressed_length(n)
+    dst = torch.empty(cap, dtype=torch.uint8, device=dev)
+    out_n = torch.zeros(1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+
+    if world > 1:
+        from compression_accelerator_b200 import multi
+        sharder = multi.ArchiveGather(ctx, dev, cap)
+
+    def step():
+        """One pass of the hot path over this rank's batch (device-resident)."""
+        ctx.compress_device(src, dst, out_n, mode=args.mode)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                sharder.exchange(dst, out_n)
+
+    def timed(fn, k):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(k):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = ctx.launches
+    parse_ms, gather_ms = [], []
+
+    def step_probe():
+        step()
+        ctx.sync()
+        parse_ms.append(ctx.stage_ms(0))
+        gather_ms.append(ctx.stage_ms(1))
+
+    ms = timed(step, args.steps)
+    launches = ctx.launches - l0
+    # a second, separately timed pass that syncs every step to read the per-kernel events
+    for _ in range(args.steps):
+        step_probe()
+    clk = clocks.stop() if rank == 0 else None
+    comp_n = int(out_n.item())
+
+    # ---- end to end through the host-pointer C-ABI entry, pinned host buffers -----------
+    pinned_out = torch.empty(cap, dtype=torch.uint8).pin_memory()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(2):
+        got = ctx.compress_into(pinned_in.data_ptr(), n, pinned_out.data_ptr(), cap, mode=args.mode)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        got = ctx.compress_into(pinned_in.data_ptr(), n, pinned_out.data_ptr(), cap, mode=args.mode)
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    assert got == comp_n, (got, comp_n)
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        pms = sorted(parse_ms)[len(parse_ms) // 2]
+        gms = sorted(gather_ms)[len(gather_ms) // 2]
+        algo = n + comp_n
+        ach = algo / (pms * 1e-3) / 1e9
+        cpu = cpu_reference(host, os.cpu_count() or 1)
+        cpu1 = cpu_reference(host, 1, budget_s=6.0)
+        cpu["single_thread_GBps"] = cpu1["value"]
+        line = {
+            "metric": "snappy_compress_input_GBps", "value": world * n * args.steps / (ms * 1e-3) / 1e9,
+            "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "mode": args.mode, "bytes_per_gpu": n,
+                       "fragments_per_gpu": n // 65536, "compressed_bytes_per_gpu": comp_n,
+                       "ratio_out_in": comp_n / n,
+                       "l2": "input (1 GiB) and staging are larger than the 126 MB L2; no flush needed",
+                       "multi_gpu": "weak: 1 GiB per rank; NCCL all_gather of sizes + payload gather on rank 0"
+                       if world > 1 else "single GPU"},
+            "roofline": {"bound": "hbm", "kernel": "parse_exact_kernel", "achieved": ach, "peak": peak,
+                         "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes": algo, "kernel_ms": pms, "scan_gather_ms": gms,
+                         "kernel_share_of_step": pms / (pms + gms) if pms + gms else None},
+            "cpu_baseline": cpu,
+            "e2e": {"value": world * n * e2e_steps / float(e2e_s.item()) / 1e9, "unit": "GB/s",
+                    "h2d_bytes_per_step": n, "d2h_bytes_per_step": comp_n + 8,
+                    "api": "snappy_b200_compress (host pointers, pinned)"},
+            "gpu_launches": launches, "clocks": clk,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="exact", choices=["exact", "fast"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

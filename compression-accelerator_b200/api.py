@@ -55,6 +55,7 @@ SYMBOLS = {
     "snappy_b200_host_free": (None, [C.c_void_p]),
     "snappy_b200_launch_count": (C.c_ulonglong, [C.c_void_p]),
     "snappy_b200_last_kernel_ms": (C.c_float, [C.c_void_p]),
+    "snappy_b200_stage_ms": (C.c_float, [C.c_void_p, C.c_int]),
     "snappy_b200_rocc_compress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
     "snappy_b200_rocc_uncompress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
 }
@@ -129,6 +130,10 @@ class Context:
     @property
     def last_kernel_ms(self) -> float:
         return lib().snappy_b200_last_kernel_ms(self._h)
+
+    def stage_ms(self, stage: int) -> float:
+        """Device ms of stage 0 (parse kernel) / 1 (scan + gather) of the last device call."""
+        return lib().snappy_b200_stage_ms(self._h, stage)
 
     def sync(self):
         _check(lib().snappy_b200_sync(self._h))

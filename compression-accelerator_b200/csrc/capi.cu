@@ -53,6 +53,8 @@ struct snappy_b200_ctx {
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t evp0 = nullptr, evp1 = nullptr, evp2 = nullptr;   // parse start / parse end / compact end
+    bool staged = false;
     unsigned long long launches = 0;
     float last_ms = 0.f;
 };
@@ -103,12 +105,16 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.sizes = (uint32_t*)c->sizes.p;
     p.n_jobs = n_frag;
     p.with_header = 0;
+    CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    CU(cudaEventRecord(c->evp1, c->stream));
     CU(sb::launch_scan((const uint32_t*)c->sizes.p, n_frag, (unsigned long long*)c->offsets.p, hdr,
                        (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
     CU(sb::launch_compact((const uint8_t*)c->staging.p, sb::kStageStride, (const uint32_t*)c->sizes.p,
                           (const unsigned long long*)c->offsets.p, n_frag, (uint8_t*)d_dst,
                           c->stream, &c->launches));
+    CU(cudaEventRecord(c->evp2, c->stream));
+    c->staged = true;
     return SNAPPY_B200_OK;
 }
 
@@ -141,6 +147,9 @@ snappy_b200_status snappy_b200_create(snappy_b200_ctx** out, int device) {
     CU(cudaMallocHost(&c->h_total, sizeof(unsigned long long)));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
+    CU(cudaEventCreate(&c->evp0));
+    CU(cudaEventCreate(&c->evp1));
+    CU(cudaEventCreate(&c->evp2));
     *out = c;
     return SNAPPY_B200_OK;
 }
@@ -155,6 +164,9 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->evp0) cudaEventDestroy(c->evp0);
+    if (c->evp1) cudaEventDestroy(c->evp1);
+    if (c->evp2) cudaEventDestroy(c->evp2);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (g_default_ctx == c) g_default_ctx = nullptr;
     delete c;
@@ -165,6 +177,14 @@ void* snappy_b200_stream(snappy_b200_ctx* c) { return c ? (void*)c->stream : nul
 unsigned long long snappy_b200_launch_count(snappy_b200_ctx* c) { return c ? c->launches : 0; }
 
 float snappy_b200_last_kernel_ms(snappy_b200_ctx* c) { return c ? c->last_ms : 0.f; }
+
+float snappy_b200_stage_ms(snappy_b200_ctx* c, int stage) {
+    if (!c || !c->staged) return 0.f;
+    float ms = 0.f;
+    cudaError_t e = stage == 0 ? cudaEventElapsedTime(&ms, c->evp0, c->evp1)
+                               : cudaEventElapsedTime(&ms, c->evp1, c->evp2);
+    return e == cudaSuccess ? ms : 0.f;
+}
 
 snappy_b200_status snappy_b200_sync(snappy_b200_ctx* c) {
     if (!c) return fail(SNAPPY_B200_INVALID_INPUT, "null ctx");
@@ -218,7 +238,11 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.sizes = d_sizes;
     p.n_jobs = (uint32_t)count;
     p.with_header = 1;
+    CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    CU(cudaEventRecord(c->evp1, c->stream));
+    CU(cudaEventRecord(c->evp2, c->stream));
+    c->staged = true;
     return SNAPPY_B200_OK;
 }
 

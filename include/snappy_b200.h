@@ -103,6 +103,11 @@ unsigned long long snappy_b200_launch_count(snappy_b200_ctx* ctx);
 /* Device time in ms of the last host-entry call's kernels (CUDA events), 0 if none. */
 float snappy_b200_last_kernel_ms(snappy_b200_ctx* ctx);
 
+/* Device time in ms (CUDA events on the context's stream) of the stages of the most recent
+ * device/batch call: stage 0 = fragment parse kernel, stage 1 = size scan + gather.  Valid
+ * after snappy_b200_sync(). */
+float snappy_b200_stage_ms(snappy_b200_ctx* ctx, int stage);
+
 /* ---- RoCC driver mirror: tests/compression.c:20-27 and :32-39.  Host pointers, blocking.
  * compress returns the compressed length (0 on failure: a valid stream is never empty);
  * uncompress returns 0 on success, non-zero on failure, as the reference documents. */

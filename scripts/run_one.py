@@ -1,0 +1,65 @@
+#!/usr/bin/env python
+"""Small driver for profiling: compress `--mib` MiB of a corpus on the device `--reps` times and
+print per-stage device times.  Used under ncu (see profiles/README.md)."""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mib", type=float, default=18.5)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--mode", default="exact")
+    ap.add_argument("--data", default="mtg", choices=["mtg", "random", "zeros", "alice"])
+    ap.add_argument("--batch", type=int, default=0, help="if >0: batch path with buffers of this many bytes")
+    ap.add_argument("--check", action="store_true")
+    a = ap.parse_args()
+    import numpy as np
+    import torch
+    import corpus
+    import __graft_entry__ as g
+    pkg = g.load_package()
+    n = int(a.mib * (1 << 20))
+    if a.data == "mtg":
+        host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)
+    elif a.data == "alice":
+        host = corpus.repeat_to(corpus.fixture("alice29.txt"), n)
+    elif a.data == "random":
+        host = corpus.random_ascii(n)
+    else:
+        host = np.full(n, 97, dtype=np.uint8)
+    ctx = pkg.Context(0)
+    src = torch.from_numpy(host).cuda()
+    if a.batch:
+        count = n // a.batch
+        for _ in range(a.reps):
+            dst, ostride, sizes = ctx.compress_batch_device(src, a.batch, a.batch, count, mode=a.mode)
+            ctx.sync()
+            ms = ctx.stage_ms(0)
+            print("batch %d x %d B: parse %.3f ms  %.2f GB/s in, out/in %.4f" % (
+                count, a.batch, ms, count * a.batch / ms / 1e6, float(sizes.sum().item()) / (count * a.batch)))
+        return
+    for _ in range(a.reps):
+        dst, out_n = ctx.compress_device(src, mode=a.mode)
+        ctx.sync()
+        p, s = ctx.stage_ms(0), ctx.stage_ms(1)
+        tot = int(out_n.item())
+        print("%s %s %.1f MiB: parse %.3f ms  gather %.3f ms  %.2f GB/s in, out/in %.4f" % (
+            a.data, a.mode, n / 2**20, p, s, n / (p + s) / 1e6, tot / n))
+    if a.check:
+        import oracle_lib
+        chk = oracle_lib.checker()
+        comp = bytes(dst[:tot].cpu().numpy())
+        if a.mode == "exact":
+            want = chk.compress(host.tobytes())
+            print("exact parity:", comp == want)
+        print("roundtrip:", chk.uncompress(comp, n) == host.tobytes())
+
+
+if __name__ == "__main__":
+    main()
