@@ -49,7 +49,7 @@ struct DevBuf {
 struct snappy_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    DevBuf staging, sizes, offsets, d_in, d_out;
+    DevBuf seqs, nseq, sizes, offsets, d_in, d_out;
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -92,27 +92,30 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
     const uint32_t hdr = with_header ? sb::varint32_len((uint32_t)n) : 0;
-    CU(c->staging.reserve((size_t)n_frag * sb::kStageStride + 256));
+    CU(c->seqs.reserve((size_t)n_frag * sb::seq_stride(sb::kBlock) * sizeof(sb::seq_t) + 256));
+    CU(c->nseq.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
     CU(c->sizes.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
     CU(c->offsets.reserve((size_t)(n_frag + 1) * sizeof(unsigned long long)));
-    sb::ParseParams p;
+    sb::JobParams p;
     p.in = (const uint8_t*)d_src;
     p.n_total = n;
     p.in_stride = sb::kBlock;
     p.job_len = sb::kBlock;
-    p.out = (uint8_t*)c->staging.p;
-    p.out_stride = sb::kStageStride;
-    p.sizes = (uint32_t*)c->sizes.p;
     p.n_jobs = n_frag;
+    p.seqs = (sb::seq_t*)c->seqs.p;
+    p.nseq = (uint32_t*)c->nseq.p;
+    p.sizes = (uint32_t*)c->sizes.p;
     p.with_header = 0;
+    p.out = (uint8_t*)d_dst;
+    p.out_stride = 0;
+    p.offsets = (const unsigned long long*)c->offsets.p;
     CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
+    CU(sb::launch_size(p, c->stream, &c->launches));
     CU(sb::launch_scan((const uint32_t*)c->sizes.p, n_frag, (unsigned long long*)c->offsets.p, hdr,
                        (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
-    CU(sb::launch_compact((const uint8_t*)c->staging.p, sb::kStageStride, (const uint32_t*)c->sizes.p,
-                          (const unsigned long long*)c->offsets.p, n_frag, (uint8_t*)d_dst,
-                          c->stream, &c->launches));
+    CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
     return SNAPPY_B200_OK;
@@ -158,7 +161,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->staging.release(); c->sizes.release(); c->offsets.release();
+    c->seqs.release(); c->nseq.release(); c->sizes.release(); c->offsets.release();
     c->d_in.release(); c->d_out.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
@@ -228,19 +231,26 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "out_stride < max_compressed_length(len)");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (count == 0) return SNAPPY_B200_OK;
-    sb::ParseParams p;
+    CU(c->seqs.reserve(count * sb::seq_stride((uint32_t)len) * sizeof(sb::seq_t) + 256));
+    CU(c->nseq.reserve((count + 1) * sizeof(uint32_t)));
+    sb::JobParams p;
     p.in = (const uint8_t*)d_src;
     p.n_total = (count - 1) * in_stride + len;
     p.in_stride = in_stride;
     p.job_len = (uint32_t)len;
+    p.n_jobs = (uint32_t)count;
+    p.seqs = (sb::seq_t*)c->seqs.p;
+    p.nseq = (uint32_t*)c->nseq.p;
+    p.sizes = d_sizes;
+    p.with_header = 1;
     p.out = (uint8_t*)d_dst;
     p.out_stride = out_stride;
-    p.sizes = d_sizes;
-    p.n_jobs = (uint32_t)count;
-    p.with_header = 1;
+    p.offsets = nullptr;
     CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
+    CU(sb::launch_size(p, c->stream, &c->launches));
+    CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
     return SNAPPY_B200_OK;

@@ -1,0 +1,138 @@
+// emit.cuh -- from sequence lists to Snappy elements.
+//   size_kernel  one warp per job: encoded bytes of the job (EmitLiteral + EmitCopy sizes,
+//                tests/snappy/snappy.cc:337-431) [+ varint header in batch mode].
+//   emit_kernel  one CTA per job: block scan of per-sequence input/output lengths, then every
+//                thread encodes its own sequence at its final output position; long literals
+//                are copied cooperatively with 16-byte stores.  Output is written once.
+#pragma once
+#include "kernels.h"
+#include "snappy_device.cuh"
+
+namespace sb {
+
+__device__ __forceinline__ uint32_t job_len_of(const JobParams& p, uint32_t job) {
+    uint64_t left = p.n_total - (uint64_t)job * p.in_stride;
+    return left < p.job_len ? (uint32_t)left : p.job_len;
+}
+
+__device__ __forceinline__ uint32_t seq_encoded_size(seq_t q) {
+    uint32_t lit = seq_lit(q), len = seq_len(q);
+    uint32_t n = lit ? literal_header_size(lit) + lit : 0;
+    if (len) n += copy_encoded_size(seq_off(q), len);
+    return n;
+}
+
+__global__ void __launch_bounds__(128) size_kernel(JobParams p) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (job >= p.n_jobs) return;
+    const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+    const uint32_t n = p.nseq[job];
+    uint32_t sum = 0;
+    for (uint32_t i = lane; i < n; i += 32) sum += seq_encoded_size(q[i]);
+    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
+    if (lane == 0) p.sizes[job] = sum + (p.with_header ? varint32_len(job_len_of(p, job)) : 0);
+}
+
+// Cooperative copy of n bytes global -> global, both arbitrarily aligned: destination-aligned
+// 16-byte stores assembled from aligned 4-byte source words (funnel shift).
+__device__ __forceinline__ void block_copy(uint8_t* __restrict__ d, const uint8_t* __restrict__ s,
+                                           uint32_t n, uint32_t tid, uint32_t nthreads) {
+    uint32_t head = (uint32_t)((16u - ((uintptr_t)d & 15u)) & 15u);
+    if (head > n) head = n;
+    if (tid < head) d[tid] = s[tid];
+    const uint32_t body = (n - head) >> 4;
+    if (body) {
+        uint4* d4 = reinterpret_cast<uint4*>(d + head);
+        const uint8_t* sb_ = s + head;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)sb_ & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)(uintptr_t)sb_ & 3u) << 3;
+        for (uint32_t j = tid; j < body; j += nthreads) {
+            const uint32_t* q = w + (j << 2);
+            uint32_t a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2), a3 = __ldg(q + 3);
+            uint32_t a4 = sh ? __ldg(q + 4) : 0u;      // never read past the source when aligned
+            uint4 v;
+            v.x = __funnelshift_r(a0, a1, sh);
+            v.y = __funnelshift_r(a1, a2, sh);
+            v.z = __funnelshift_r(a2, a3, sh);
+            v.w = __funnelshift_r(a3, a4, sh);
+            d4[j] = v;
+        }
+    }
+    const uint32_t done = head + (body << 4);
+    if (done + tid < n) d[done + tid] = s[done + tid];
+}
+
+constexpr int kEmitThreads = 256;
+constexpr uint32_t kShortLiteral = 32;   // literals up to this many bytes are copied by their thread
+constexpr int kMaxLong = kEmitThreads;   // long-literal work items per tile
+
+__global__ void __launch_bounds__(kEmitThreads) emit_kernel(JobParams p) {
+    __shared__ unsigned long long warp_tot[kEmitThreads / 32];
+    __shared__ unsigned long long carry_s;
+    __shared__ uint32_t long_src[kMaxLong], long_dst[kMaxLong], long_len[kMaxLong];
+    __shared__ uint32_t n_long;
+    const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t len = job_len_of(p, job);
+    const uint8_t* __restrict__ in = p.in + (uint64_t)job * p.in_stride;
+    uint8_t* __restrict__ out = p.out + (p.offsets ? p.offsets[job] : (uint64_t)job * p.out_stride);
+    const seq_t* __restrict__ q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+    const uint32_t n = p.nseq[job];
+    uint32_t hdr = 0;
+    if (p.with_header) {
+        hdr = varint32_len(len);
+        if (tid == 0) put_varint32(out, len);
+    }
+    if (tid == 0) { carry_s = (unsigned long long)hdr; n_long = 0; }   // hi32 = input pos, lo32 = output pos
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += kEmitThreads) {
+        const uint32_t i = base + tid;
+        seq_t sq = i < n ? q[i] : 0ull;
+        const uint32_t lit = seq_lit(sq), clen = seq_len(sq), off = seq_off(sq);
+        const uint32_t lh = lit ? literal_header_size(lit) : 0;
+        const uint32_t osz = lh + lit + (clen ? copy_encoded_size(off, clen) : 0);
+        unsigned long long v = ((unsigned long long)(lit + clen) << 32) | osz, x = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long y = __shfl_up_sync(kFull, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) warp_tot[wid] = x;
+        __syncthreads();
+        unsigned long long pre = carry_s;
+        for (uint32_t k = 0; k < wid; ++k) pre += warp_tot[k];
+        const unsigned long long excl = pre + x - v;
+        const uint32_t ipos = (uint32_t)(excl >> 32);
+        uint32_t op = (uint32_t)excl;
+        if (lit) {                                           // snappy.cc:337-378 EmitLiteral
+            const uint32_t m = lit - 1;
+            if (m < 60) out[op] = (uint8_t)(m << 2);
+            else if (m < 256) { out[op] = 60u << 2; out[op + 1] = (uint8_t)m; }
+            else { out[op] = 61u << 2; out[op + 1] = (uint8_t)m; out[op + 2] = (uint8_t)(m >> 8); }
+            op += lh;
+            if (lit <= kShortLiteral) {
+                for (uint32_t b = 0; b < lit; ++b) out[op + b] = __ldg(in + ipos + b);
+            } else {
+                uint32_t slot = atomicAdd(&n_long, 1u);
+                long_src[slot] = ipos; long_dst[slot] = op; long_len[slot] = lit;
+            }
+            op += lit;
+        }
+        if (clen) {                                          // snappy.cc:402-431 EmitCopy
+            uint32_t rem = clen;
+            if (rem >= 12) {
+                while (rem >= 68) { op += put_copy_le64(out + op, off, 64, false); rem -= 64; }
+                if (rem > 64) { op += put_copy_le64(out + op, off, 60, false); rem -= 60; }
+            }
+            put_copy_le64(out + op, off, rem, rem < 12);
+        }
+        __syncthreads();
+        const uint32_t nl = n_long;
+        for (uint32_t k = 0; k < nl; ++k)
+            block_copy(out + long_dst[k], in + long_src[k], long_len[k], tid, kEmitThreads);
+        __syncthreads();
+        if (tid == kEmitThreads - 1) { carry_s = excl + v; n_long = 0; }
+        __syncthreads();
+    }
+}
+
+}  // namespace sb

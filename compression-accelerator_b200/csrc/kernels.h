@@ -1,39 +1,58 @@
 // kernels.h -- host-side launchers of the Snappy kernels (internal to libsnappy_b200).
+//
+// Pipeline of one call (all on one stream):
+//   parse   one warp-group per fragment: greedy parse -> list of sequences (literal run, copy)
+//   size    encoded size of every fragment from its sequence list
+//   scan    exclusive scan of sizes (+ varint header) -> output offset of every fragment
+//   emit    sequences + input -> Snappy elements written ONCE at their final position
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace sb {
 
-// Per-fragment staging stride in the stream path: MaxCompressedLength(65536) = 76490
-// (tests/snappy/snappy.cc:99-121) rounded up to a multiple of 128.
-constexpr uint32_t kStageStride = 76544;
+// A sequence = literal run followed by one copy (the unit EmitLiteral + EmitCopy produce per
+// match in tests/snappy/snappy.cc:614-641).  Packed in a uint64:
+//   bits  0..16  lit_len   (0..65536)   bytes of literal before the copy
+//   bits 17..32  copy_len  (0, 4..65535) 0 = no copy (the fragment's trailing literal)
+//   bits 33..48  offset    (1..65535)
+typedef unsigned long long seq_t;
+__host__ __device__ inline seq_t seq_pack(uint32_t lit, uint32_t len, uint32_t off) {
+    return (seq_t)lit | ((seq_t)len << 17) | ((seq_t)off << 33);
+}
+__host__ __device__ inline uint32_t seq_lit(seq_t s) { return (uint32_t)s & 0x1ffffu; }
+__host__ __device__ inline uint32_t seq_len(seq_t s) { return (uint32_t)(s >> 17) & 0xffffu; }
+__host__ __device__ inline uint32_t seq_off(seq_t s) { return (uint32_t)(s >> 33) & 0xffffu; }
 
-// One "job" = one fragment / one small buffer, parsed by one warp.
-struct ParseParams {
+// Sequences a job of `job_len` input bytes can produce: every copy consumes >= 4 bytes.
+__host__ __device__ inline uint32_t seq_stride(uint32_t job_len) { return job_len / 4 + 8; }
+
+// One "job" = one fragment of a stream, or one small buffer of a batch.
+struct JobParams {
     const uint8_t* in;     // job j reads in + j*in_stride
     uint64_t n_total;      // bytes reachable from `in` (job length = min(job_len, n_total - j*in_stride))
     uint64_t in_stride;
     uint32_t job_len;      // 65536 in the stream path, buffer length in the batch path
-    uint8_t* out;          // job j writes out + j*out_stride
-    uint64_t out_stride;
-    uint32_t* sizes;       // sizes[j] = bytes written by job j (header included when with_header)
     uint32_t n_jobs;
+    seq_t* seqs;           // job j's sequences at seqs + j*seq_stride(job_len)
+    uint32_t* nseq;        // number of sequences of job j
+    uint32_t* sizes;       // encoded bytes of job j (header included when with_header)
     uint32_t with_header;  // 1: each job is its own stream and starts with varint32(len)
+    // emit destination: job j writes at out + (offsets ? offsets[j] : j*out_stride)
+    uint8_t* out;
+    uint64_t out_stride;
+    const unsigned long long* offsets;
 };
 
-cudaError_t launch_parse(const ParseParams& p, int mode, cudaStream_t st, unsigned long long* launches);
+cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned long long* launches);
+cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
+cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 
 // Exclusive scan of sizes[0..n_frag) (+hdr_len) into offsets (uint64), total stream length into
 // *d_total; writes varint32(n_input) at dst when hdr_len > 0.
 cudaError_t launch_scan(const uint32_t* sizes, uint32_t n_frag, unsigned long long* offsets,
                         uint32_t hdr_len, uint32_t n_input, uint8_t* dst,
                         unsigned long long* d_total, cudaStream_t st, unsigned long long* launches);
-
-// Gather staged fragment outputs into the final contiguous stream.
-cudaError_t launch_compact(const uint8_t* staging, uint64_t stage_stride, const uint32_t* sizes,
-                           const unsigned long long* offsets, uint32_t n_frag, uint8_t* dst,
-                           cudaStream_t st, unsigned long long* launches);
 
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 
