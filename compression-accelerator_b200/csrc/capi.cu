@@ -85,7 +85,7 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
                                 size_t dst_cap, unsigned long long* d_out_n, int mode,
                                 bool with_header) {
     if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
-    if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST)
+    if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */)
         return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
     if (dst_cap < snappy_b200_max_compressed_length(n) - (with_header ? 0 : 0))
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");

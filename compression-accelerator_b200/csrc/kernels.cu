@@ -9,6 +9,7 @@
 #include "kernels.h"
 #include "snappy_device.cuh"
 #include "parse_serial.cuh"
+#include "parse_window.cuh"
 #include "emit.cuh"
 
 namespace sb {
@@ -17,8 +18,13 @@ namespace sb {
 constexpr uint32_t kSmemTableOff = 128;
 constexpr uint32_t kInputPad = 32;   // slack so unaligned word reads past the end stay in bounds
 
+// peer-detector scratch (parse_window.cuh): fewer slots for small jobs so more of them fit an SM
+__host__ __device__ inline uint32_t peer_slots(uint32_t job_len) {
+    return job_len > 16384 ? kPeerSlots : 512u;
+}
 __host__ __device__ inline uint32_t parse_smem_bytes(uint32_t job_len) {
-    return kSmemTableOff + table_entries(job_len) * 2 + ((job_len + 15u) & ~15u) + kInputPad;
+    return kSmemTableOff + table_entries(job_len) * 2 + peer_slots(job_len) * 4 +
+           ((job_len + 15u) & ~15u) + kInputPad;
 }
 
 // Stage src[0,len) into shared memory: TMA bulk copy for the 16-byte-aligned body, ordinary
@@ -46,7 +52,8 @@ __device__ __forceinline__ void stage_fragment(const uint8_t* __restrict__ src, 
     if (bulk) mbar_wait(bar, 0);
 }
 
-__global__ void __launch_bounds__(32) parse_serial_kernel(JobParams p) {
+template <bool kWindow>
+__global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int lane = threadIdx.x;
     const uint32_t job = blockIdx.x;
@@ -54,11 +61,15 @@ __global__ void __launch_bounds__(32) parse_serial_kernel(JobParams p) {
     uint16_t* table = reinterpret_cast<uint16_t*>(smem + kSmemTableOff);
     const uint32_t len = job_len_of(p, job);
     const uint32_t entries = table_entries(len);            // from THIS fragment's length
-    uint8_t* s_in = smem + kSmemTableOff + table_entries(p.job_len) * 2;
+    uint32_t* scr = reinterpret_cast<uint32_t*>(smem + kSmemTableOff + table_entries(p.job_len) * 2);
+    const uint32_t nscr = peer_slots(p.job_len);
+    uint8_t* s_in = reinterpret_cast<uint8_t*>(scr + nscr);
+    if (kWindow) for (uint32_t i = lane; i < nscr; i += 32) scr[i] = kFull;
     stage_fragment(p.in + (uint64_t)job * p.in_stride, len, s_in, table, entries, bar, lane);
     SeqWriter out{p.seqs + (uint64_t)job * seq_stride(p.job_len), 0};
     const int shift = 32 - (31 - __clz(entries));           // snappy.cc:548
-    parse_fragment_serial(s_in, len, table, shift, out, lane);
+    if (kWindow) parse_fragment_window(s_in, len, table, scr, nscr - 1, shift, out, lane);
+    else parse_fragment_serial(s_in, len, table, shift, out, lane);
     if (lane == 0) p.nseq[job] = out.n;
 }
 
@@ -105,15 +116,18 @@ __global__ void __launch_bounds__(1024) scan_sizes_kernel(const uint32_t* __rest
 
 // ---- launchers ----------------------------------------------------------------------------------
 cudaError_t kernels_init() {
-    return cudaFuncSetAttribute(parse_serial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)parse_smem_bytes(kBlock));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)parse_smem_bytes(kBlock));
 }
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
                          unsigned long long* launches) {
-    (void)mode;
     if (p.n_jobs == 0) return cudaSuccess;
-    parse_serial_kernel<<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
+    if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
+    else parse_kernel<true><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

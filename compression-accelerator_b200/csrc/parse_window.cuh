@@ -1,0 +1,231 @@
+// parse_window.cuh -- lane-parallel restatement of Snappy's greedy parse, byte-exact.
+//
+// The fragment is cut into aligned windows of 32 positions; lane k of the warp owns position
+// 32*win + k.  Per window the lanes do, in parallel, everything that does not depend on the
+// parse: load the 4-byte word, hash it (tests/snappy/snappy.cc:91-97), look the hash table up,
+// compare with the candidate (:607), pre-extend the match by up to 12 bytes
+// (snappy-internal.h:95-143) and -- assuming the copy at their position is taken -- work out
+// where the parse goes next (:643-659: the copy's end, then the next position whose probe
+// hits).  The sequential part of the parse is then a pointer chase over those per-lane "next"
+// values: one warp shuffle per COPY, no shared-memory access on its critical path.
+//
+// Exactness.  A probe's candidate is the most recent insert with its hash.  Inserts of earlier
+// windows are in the table when a window is entered.  Inserts made inside the window can only
+// shadow the table entry of a lane that shares its hash with a lower lane ("peer" lanes, found
+// with a shared-memory min-scatter); those lanes, and matches longer than the 12 pre-extended
+// bytes, are evaluated exactly when the chase reaches them (slow path).  Table inserts (:606,
+// :649-655) are kept as a lane mask and committed when the parse leaves the window, the highest
+// lane per slot winning as in serial order.  Scans that miss 32 times in a row (skip >= 64,
+// step > 1, :590-597) fall back to the serial scan.
+#pragma once
+#include "parse_serial.cuh"
+
+namespace sb {
+
+constexpr uint32_t kPeerSlots = 2048;   // uint32 scratch slots of the peer detector (stream path)
+
+// five aligned words starting at the word containing `pos` -> the 16 bytes at pos..pos+15
+__device__ __forceinline__ void lds16u(const uint8_t* s, uint32_t pos, uint32_t& b0, uint32_t& b1,
+                                       uint32_t& b2, uint32_t& b3) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(s) + (pos >> 2);
+    const uint32_t sh = (pos & 3u) << 3;
+    uint32_t a0 = w[0], a1 = w[1], a2 = w[2], a3 = w[3], a4 = w[4];
+    b0 = __funnelshift_r(a0, a1, sh);
+    b1 = __funnelshift_r(a1, a2, sh);
+    b2 = __funnelshift_r(a2, a3, sh);
+    b3 = __funnelshift_r(a3, a4, sh);
+}
+
+__device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return s >= 32 ? 0u : (kFull << s); }
+__device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return e >= 32 ? kFull : ((1u << e) - 1u); }
+
+// Write the pending inserts `I` of a window: table[h] = pos for every inserted lane, the highest
+// lane of a hash slot winning.  Without peers in the window no two lanes share a slot.
+__device__ __forceinline__ void window_commit(uint16_t* table, uint32_t h, uint32_t pos, uint32_t I,
+                                              bool any_peer, int lane) {
+    bool pending = (I >> lane) & 1u;
+    if (pending) table[h] = (uint16_t)pos;
+    __syncwarp();
+    if (any_peer) {
+        for (;;) {
+            bool redo = pending && table[h] < pos;          // a lower lane's store landed last
+            if (!__any_sync(kFull, redo)) break;
+            pending = redo;
+            if (pending) table[h] = (uint16_t)pos;
+            __syncwarp();
+        }
+    }
+}
+
+struct WindowParser {
+    const uint8_t* s;
+    uint32_t len, ip_limit;
+    uint16_t* table;
+    uint32_t* scr;          // peer-detector scratch, all 0xffffffff between windows
+    uint32_t scr_mask;
+    int shift, lane;
+    SeqWriter* out;
+    uint32_t next_emit;
+
+    // per-window lane registers
+    uint32_t pos, h, T, ml, ek, nx, Sk;
+
+    // Store the sequences of the fast copies in `chosen` (lane order = stream order).
+    __device__ __forceinline__ void flush_chosen(uint32_t chosen, uint32_t lt) {
+        const uint32_t prevmask = chosen & lt;
+        const uint32_t prev = prevmask ? 31u - __clz(prevmask) : 0u;
+        const uint32_t e_prev = __shfl_sync(kFull, ek, prev);
+        if ((chosen >> lane) & 1u) {
+            const uint32_t lit = prevmask ? (uint32_t)lane - e_prev : pos - next_emit;
+            out->seqs[out->n + __popc(prevmask)] = seq_pack(lit, 4 + ml, pos - T);
+        }
+        out->n += __popc(chosen);
+    }
+
+    __device__ __forceinline__ void run() {
+        const uint32_t lt = (1u << lane) - 1u;
+        uint32_t win = 0, sl = 1, I = 0;                    // first probe is position 1 (:560)
+        int scan0 = 1;                                      // lane of probe #0 of the current scan
+        for (;;) {                                          // one iteration per window
+            // ---- parallel set-up -----------------------------------------------------------
+            const uint32_t wbase = win << 5;
+            pos = wbase + lane;
+            uint32_t d0, d1, d2, d3;
+            lds16u(s, pos, d0, d1, d2, d3);
+            h = hash32(d0, shift);
+            T = table[h];
+            uint32_t* slot = scr + (h & scr_mask);
+            atomicMin(slot, (uint32_t)lane);
+            uint32_t c0, c1, c2, c3;
+            lds16u(s, T, c0, c1, c2, c3);
+            __syncwarp();
+            const bool peer = *slot != (uint32_t)lane;      // a lower lane has my hash (or aliases it)
+            const bool hit = (c0 == d0);
+            {
+                uint32_t x1 = c1 ^ d1, x2 = c2 ^ d2, x3 = c3 ^ d3, m = 12;
+                if (x3) m = 8 + ((uint32_t)(__ffs(x3) - 1) >> 3);
+                if (x2) m = 4 + ((uint32_t)(__ffs(x2) - 1) >> 3);
+                if (x1) m = (uint32_t)(__ffs(x1) - 1) >> 3;
+                ml = m;
+            }
+            __syncwarp();
+            *slot = kFull;                                  // reset the detector for the next window
+            const uint32_t inval = ~__ballot_sync(kFull, pos < ip_limit);
+            const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;   // first lane past ip_limit
+            const uint32_t VPRE = lanes_below(vpre_end);
+            const uint32_t L = __ballot_sync(kFull, hit || peer) & VPRE;           // lanes whose probe may hit
+            const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == 12);
+            const bool any_peer = __any_sync(kFull, peer);
+            ek = lane + 4 + ml;                              // lane of ip after taking my copy
+            {
+                const uint32_t ipk = pos + 4 + ml;
+                uint32_t v;
+                if (ipk >= ip_limit) v = 256;                // parse ends after my copy (:643-645)
+                else if (ek >= 32) v = 64u | (ek - 32);      // my copy leaves the window
+                else {
+                    const uint32_t m = L & (kFull << ek);
+                    if (!m) v = 32;                          // no further hit in this window
+                    else { v = __ffs(m) - 1; if ((SLOWM >> v) & 1u) v |= 128u; }
+                }
+                nx = v;
+                const uint32_t last_skipped = ek - 1 < 32 ? ek - 1 : 32;   // lanes lane+1 .. ek-2 are not inserted
+                Sk = lanes_below(last_skipped) & ~((2u << lane) - 1u);
+            }
+            // ---- sequential part: chase the copies of this window ------------------------------
+            bool done_window = false;
+            while (!done_window) {
+                const uint32_t vend0 = scan0 < 0 ? (uint32_t)(scan0 + 32) : 32u;  // step-1 regime ends here
+                const uint32_t m0 = L & lanes_from(sl) & lanes_below(vend0);
+                uint32_t f = 32, last = 32, chosen = 0;
+                if (m0) { f = __ffs(m0) - 1; if ((SLOWM >> f) & 1u) f |= 128u; }
+                while (f < 32) {
+                    chosen |= 1u << f;
+                    last = f;
+                    f = __shfl_sync(kFull, nx, f);
+                }
+                const uint32_t SK = __reduce_or_sync(kFull, ((chosen >> lane) & 1u) ? Sk : 0u);
+                uint32_t e_last = 0;
+                if (chosen) {
+                    e_last = __shfl_sync(kFull, ek, last);
+                    flush_chosen(chosen, lt);
+                    next_emit = wbase + e_last;
+                    scan0 = (int)e_last + 1;
+                }
+                if (f == 32) {                               // no more hits: the scan runs off its range
+                    const uint32_t vend = chosen ? 32u : vend0;
+                    const uint32_t upto = vend < vpre_end ? vend : vpre_end;
+                    I |= lanes_from(sl) & lanes_below(upto) & ~SK;
+                    if (vpre_end <= vend && inval) return;   // next probe would pass ip_limit (:598)
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    if (vend < 32) {                         // 32 misses in a row: skip reached 64
+                        uint32_t ip = wbase + vend, skip = 64, cand;
+                        if (!serial_scan(s, table, shift, ip_limit, ip, skip, cand)) return;
+                        const uint32_t matched = 4 + warp_match_len(s, cand + 4, ip + 4, len, lane);
+                        out->push(ip - next_emit, matched, ip - cand, lane);
+                        ip += matched;
+                        next_emit = ip;
+                        if (ip >= ip_limit) return;
+                        const uint32_t a = (ip - 1) & 31u;
+                        win = (ip - 1) >> 5; I = 1u << a; sl = a + 1; scan0 = (int)a + 2;
+                    } else {
+                        win += 1; sl = 0; scan0 -= 32; I = 0;
+                    }
+                    done_window = true;
+                } else if (f & 256u) {                       // last copy reached the end margin
+                    return;
+                } else if (f & 64u) {                        // last copy leaves the window
+                    I |= lanes_from(sl) & ~SK;
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    const uint32_t ip = next_emit;
+                    if (e_last == 32) { win += 1; sl = 0; scan0 = 1; I = 0; }
+                    else {
+                        const uint32_t a = (ip - 1) & 31u;
+                        win = (ip - 1) >> 5; I = 1u << a; sl = a + 1; scan0 = (int)a + 2;
+                    }
+                    done_window = true;
+                } else {                                     // exact evaluation of lane fs
+                    const uint32_t fs = f & 31u;
+                    I |= lanes_from(sl) & lanes_below(fs) & ~SK;
+                    const uint32_t sameh = __ballot_sync(kFull, h == __shfl_sync(kFull, h, fs));
+                    const uint32_t pk = sameh & I & lanes_below(fs);     // inserted peers, serial order
+                    const uint32_t cand = pk ? wbase + (31u - __clz(pk)) : __shfl_sync(kFull, T, fs);
+                    const uint32_t p = wbase + fs;
+                    I |= 1u << fs;
+                    if (lds32u(s, cand) != lds32u(s, p)) { sl = fs + 1; continue; }   // missed probe (:607)
+                    const uint32_t matched = 4 + warp_match_len(s, cand + 4, p + 4, len, lane);
+                    out->push(p - next_emit, matched, p - cand, lane);
+                    const uint32_t ip = p + matched;
+                    next_emit = ip;
+                    if (ip >= ip_limit) return;
+                    const uint32_t e = ip - wbase;
+                    if (e <= 32) I |= 1u << (e - 1);         // insert ip-1 (:649-651)
+                    if (e < 32) { sl = e; scan0 = (int)e + 1; continue; }
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    if (e == 32) { win += 1; sl = 0; scan0 = 1; I = 0; }
+                    else {
+                        const uint32_t a = (ip - 1) & 31u;
+                        win = (ip - 1) >> 5; I = 1u << a; sl = a + 1; scan0 = (int)a + 2;
+                    }
+                    done_window = true;
+                }
+            }
+        }
+    }
+};
+
+__device__ __forceinline__ void parse_fragment_window(const uint8_t* s, uint32_t len,
+                                                      uint16_t* table, uint32_t* scr,
+                                                      uint32_t scr_mask, int shift, SeqWriter& out,
+                                                      int lane) {
+    WindowParser wp;
+    wp.next_emit = 0;
+    if (len >= kMargin) {                                   // snappy.cc:557
+        wp.s = s; wp.len = len; wp.ip_limit = len - kMargin;   // :558
+        wp.table = table; wp.scr = scr; wp.scr_mask = scr_mask;
+        wp.shift = shift; wp.lane = lane; wp.out = &out;
+        wp.run();
+    }
+    if (wp.next_emit < len) out.push(len - wp.next_emit, 0, 0, lane);   // :665-668
+}
+
+}  // namespace sb
