@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <new>
@@ -61,6 +62,10 @@ struct snappy_b200_ctx {
 
 namespace {
 
+// SNAPPY_B200_DEBUG=1: after the parse, validate the sequence lists on the device and fail the
+// call (before anything is emitted) if a job's lengths do not add up.
+snappy_b200_status debug_check(snappy_b200_ctx* c, const sb::JobParams& p);
+
 std::once_flag g_init_once;
 cudaError_t g_init_err = cudaSuccess;
 
@@ -85,7 +90,8 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
                                 size_t dst_cap, unsigned long long* d_out_n, int mode,
                                 bool with_header) {
     if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
-    if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */)
+    if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */ &&
+        mode != 3 /* exact, single-warp window parser */ && mode != 4 /* exact, pipelined, input in smem */)
         return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
     if (dst_cap < snappy_b200_max_compressed_length(n) - (with_header ? 0 : 0))
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");
@@ -112,12 +118,34 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
+    if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(sb::launch_size(p, c->stream, &c->launches));
     CU(sb::launch_scan((const uint32_t*)c->sizes.p, n_frag, (unsigned long long*)c->offsets.p, hdr,
                        (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
     CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status debug_check(snappy_b200_ctx* c, const sb::JobParams& p) {
+    static const bool on = [] { const char* e = getenv("SNAPPY_B200_DEBUG"); return e && *e == '1'; }();
+    if (!on) return SNAPPY_B200_OK;
+    unsigned long long* d_rep = nullptr;
+    unsigned long long h_rep[8] = {0};
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaMalloc(&d_rep, sizeof h_rep));
+    CU(cudaMemsetAsync(d_rep, 0, sizeof h_rep, c->stream));
+    CU(sb::launch_check(p, d_rep, c->stream));
+    CU(cudaMemcpyAsync(h_rep, d_rep, sizeof h_rep, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(d_rep);
+    if (h_rep[0]) {
+        snprintf(g_err, sizeof g_err, "debug: %llu bad sequence lists; first job %llu nseq %llu sum %llu len %llu",
+                 h_rep[0], h_rep[1], h_rep[2], h_rep[3], h_rep[4]);
+        fprintf(stderr, "libsnappy_b200 %s\n", g_err);
+        return SNAPPY_B200_CUDA_ERROR;
+    }
     return SNAPPY_B200_OK;
 }
 
@@ -249,6 +277,7 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     CU(cudaEventRecord(c->evp0, c->stream));
     CU(sb::launch_parse(p, mode, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
+    if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(sb::launch_size(p, c->stream, &c->launches));
     CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));

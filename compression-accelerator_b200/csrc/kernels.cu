@@ -10,7 +10,9 @@
 #include "snappy_device.cuh"
 #include "parse_serial.cuh"
 #include "parse_window.cuh"
+#include "parse_pipe.cuh"
 #include "emit.cuh"
+#include <type_traits>
 
 namespace sb {
 
@@ -73,6 +75,88 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     if (lane == 0) p.nseq[job] = out.n;
 }
 
+// ---- pipelined parser: one resolver warp + P producer warps per fragment ----------------------
+// kGlobal = false: fragment staged in shared memory by TMA (2 fragments per SM).
+// kGlobal = true : producers gather the input from global memory; shared memory holds only the
+//                  table and the ring (up to 6 fragments per SM).
+template <bool kGlobal> struct PipeCfg;
+template <> struct PipeCfg<false> { static constexpr uint32_t P = 2, R = 8; };
+template <> struct PipeCfg<true>  { static constexpr uint32_t P = 3, R = 6; };
+
+template <bool kGlobal>
+__host__ __device__ inline uint32_t pipe_smem_bytes(uint32_t job_len) {
+    uint32_t n = kSmemTableOff + table_entries(job_len) * 2 + (uint32_t)sizeof(PipeShared<PipeCfg<kGlobal>::R>);
+    if (!kGlobal) n += ((job_len + 15u) & ~15u) + kInputPad;
+    return n;
+}
+
+template <bool kGlobal>
+__global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_kernel(JobParams p) {
+    constexpr uint32_t P = PipeCfg<kGlobal>::P, R = PipeCfg<kGlobal>::R, NT = 32 * (1 + P);
+    static_assert(R % P == 0, "one producer must own all windows of a ring slot");
+    typedef PipeShared<R> Ring;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t job = blockIdx.x;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+    uint16_t* table = reinterpret_cast<uint16_t*>(smem + kSmemTableOff);
+    Ring* ps = reinterpret_cast<Ring*>(smem + kSmemTableOff + table_entries(p.job_len) * 2);
+    uint8_t* s_in = reinterpret_cast<uint8_t*>(ps + 1);
+    const uint32_t len = job_len_of(p, job);
+    const uint32_t entries = table_entries(len);
+    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
+
+    uint32_t bulk = 0;
+    if (!kGlobal) {                                         // TMA bulk copy of the 16-byte aligned body
+        bulk = (((uintptr_t)src & 15u) == 0) ? (len & ~15u) : 0u;
+        if (tid == 0 && bulk) {
+            mbar_init(bar, 1);
+            mbar_expect_tx(bar, bulk);
+            tma_load_1d(s_in, src, bulk, bar);
+        }
+    }
+    {
+        uint4* t4 = reinterpret_cast<uint4*>(table);
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (uint32_t i = tid; i < entries / 8; i += NT) t4[i] = z;
+        if (!kGlobal) {
+            for (uint32_t i = bulk + tid; i < len; i += NT) s_in[i] = src[i];
+            const uint32_t padded = ((len + 15u) & ~15u) + kInputPad;
+            for (uint32_t i = len + tid; i < padded; i += NT) s_in[i] = 0;
+        }
+        if (tid < R) ps->ready[tid] = 0;
+        if (tid == 0) ps->cur_win = 0;
+    }
+    __syncthreads();
+    if (bulk) mbar_wait(bar, 0);
+
+    typedef typename std::conditional<kGlobal, GlobalSrc, SmemSrc>::type Src;
+    Src in_src;
+    if constexpr (kGlobal) in_src.g = src; else in_src.s = s_in;
+    const int shift = 32 - (31 - __clz(entries));
+    // spread the resolver warps of co-resident CTAs over the SM's four schedulers
+    const uint32_t rwarp = (blockIdx.x / 148u) % (1 + P);
+    if (wid == rwarp) {
+        PipeResolver<Src, R> pr;
+        pr.next_emit = 0;
+        pr.seqs = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+        pr.nseq = 0;
+        pr.lane = (int)lane;
+        if (len >= kMargin) {
+            pr.src = in_src; pr.len = len; pr.ip_limit = len - kMargin;
+            pr.table = table; pr.ps = ps; pr.shift = shift;
+            pr.run();
+        }
+        __syncwarp();
+        if (lane == 0) ps->cur_win = kDone;
+        if (pr.next_emit < len) pr.push(len - pr.next_emit, 0, 0);
+        if (lane == 0) p.nseq[job] = pr.nseq;
+    } else if (len >= kMargin) {
+        const uint32_t pidx = wid > rwarp ? wid - 1 : wid;
+        pipe_producer<Src, R>(in_src, table, shift, len - kMargin, (len + 31) >> 5, ps, pidx, P, (int)lane);
+    }
+}
+
 // ---- scan of fragment sizes + header ---------------------------------------------------------
 __global__ void __launch_bounds__(1024) scan_sizes_kernel(const uint32_t* __restrict__ sizes,
                                                           uint32_t n, unsigned long long* offsets,
@@ -114,19 +198,57 @@ __global__ void __launch_bounds__(1024) scan_sizes_kernel(const uint32_t* __rest
     if (tid == 0) *d_total = carry_s;
 }
 
+// ---- debug self-check of the sequence lists (SNAPPY_B200_DEBUG=1) -----------------------------
+// report[0] = number of bad jobs, report[1..4] = first bad job: index, nseq, sum of lengths, len
+__global__ void __launch_bounds__(128) check_seqs_kernel(JobParams p, unsigned long long* report) {
+    const uint32_t job = blockIdx.x * 128 + threadIdx.x;
+    if (job >= p.n_jobs) return;
+    const uint32_t len = job_len_of(p, job), n = p.nseq[job], cap = seq_stride(p.job_len);
+    const seq_t* q = p.seqs + (uint64_t)job * cap;
+    unsigned long long sum = 0;
+    bool bad = n > cap;
+    for (uint32_t i = 0; i < n && !bad; ++i) {
+        const uint32_t lit = seq_lit(q[i]), cl = seq_len(q[i]), off = seq_off(q[i]);
+        if (cl && (cl < 4 || off == 0 || off > sum + lit)) bad = true;
+        if (!cl && i + 1 != n) bad = true;
+        sum += lit + cl;
+        if (sum > len) bad = true;
+    }
+    if (sum != len) bad = true;
+    if (bad && atomicAdd(report, 1ull) == 0) {
+        report[1] = job; report[2] = n; report[3] = sum; report[4] = len;
+    }
+}
+
+cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStream_t st) {
+    if (p.n_jobs == 0) return cudaSuccess;
+    check_seqs_kernel<<<(p.n_jobs + 127) / 128, 128, 0, st>>>(p, report);
+    return cudaGetLastError();
+}
+
 // ---- launchers ----------------------------------------------------------------------------------
 cudaError_t kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)parse_smem_bytes(kBlock));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)parse_smem_bytes(kBlock));
+    e = cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)parse_smem_bytes(kBlock));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(parse_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)pipe_smem_bytes<false>(kBlock));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(parse_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)pipe_smem_bytes<true>(kBlock));
 }
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
                          unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
     if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
+    else if (mode == 0)
+        parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
+    else if (mode == 4)
+        parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);
     else parse_kernel<true><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();

@@ -54,6 +54,9 @@ cudaError_t launch_scan(const uint32_t* sizes, uint32_t n_frag, unsigned long lo
                         uint32_t hdr_len, uint32_t n_input, uint8_t* dst,
                         unsigned long long* d_total, cudaStream_t st, unsigned long long* launches);
 
+// Debug: validate every job's sequence list (lengths add up, offsets in range).
+cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStream_t st);
+
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 
 }  // namespace sb

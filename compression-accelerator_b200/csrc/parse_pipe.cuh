@@ -1,0 +1,316 @@
+// parse_pipe.cuh -- the window parser of parse_window.cuh split over cooperating warps.
+//
+// A single warp per fragment is latency-bound: every instruction of the per-window set-up sits on
+// the parse's critical path.  Here P "producer" warps run ahead of one "resolver" warp.  A
+// producer does, for window w, the whole parallel set-up of parse_window.cuh (word, hash, table
+// look-up, 4-byte compare, 12-byte pre-extension, peer detection, per-lane next-copy values) and
+// leaves the result in a small shared-memory ring.  Its table look-ups are SPECULATIVE: inserts of
+// windows the resolver has not finished yet are missing.  The resolver therefore re-reads
+// table[h] for every lane when it enters the window (all earlier inserts are committed by then);
+// lanes whose entry moved are simply marked for exact evaluation, which happens only if the parse
+// actually reaches them.  The resolver itself never reads input bytes on its fast path, so the
+// input does not have to live in shared memory: with GlobalSrc the producers gather it from
+// global memory (latency hidden by running ahead) and a fragment needs only its 32 KB table plus
+// the ring -- six fragments per SM instead of two.  Bytes produced are identical to the serial
+// parse (tests/snappy/snappy.cc:539-671) by the same argument as parse_window.cuh.
+//
+// Ring protocol (per fragment): slot = w % R, R % P == 0 so one producer owns all windows of a
+// slot.  Producer p takes the smallest w >= cur_win with w % P == p, waits until w < cur_win + R,
+// fills the slot, then publishes ready[slot] = w + 1.  The resolver publishes cur_win whenever it
+// moves to another window (also when a long copy jumps over several) and kDone at the end.
+#pragma once
+#include "parse_window.cuh"
+
+namespace sb {
+
+constexpr uint32_t kDone = 0xffffffffu;
+
+// ---- input accessors ------------------------------------------------------------------------
+struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
+    const uint8_t* s;
+    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const { return lds32u(s, pos); }
+    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t) const { return lds32u(s, pos); }
+    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
+                                         uint32_t& b3) const { lds16u(s, pos, b0, b1, b2, b3); }
+};
+
+struct GlobalSrc {                       // fragment read in place from global memory
+    const uint8_t* g;                    // fragment start (any alignment)
+    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)a & 3u) << 3;
+        const uint32_t a0 = __ldg(w), a1 = sh ? __ldg(w + 1) : 0u;
+        return __funnelshift_r(a0, a1, sh);
+    }
+    // as ld32, but never touches a word that lies entirely at or beyond position `end` (the
+    // last fragment may end on the last mapped byte of the caller's buffer)
+    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t end) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t r = (uint32_t)a & 3u;
+        const uint32_t a0 = __ldg(w), a1 = (r && pos + 4 - r < end) ? __ldg(w + 1) : 0u;
+        return __funnelshift_r(a0, a1, r << 3);
+    }
+    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
+                                         uint32_t& b3) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)a & 3u) << 3;
+        const uint32_t a0 = __ldg(w), a1 = __ldg(w + 1), a2 = __ldg(w + 2), a3 = __ldg(w + 3);
+        const uint32_t a4 = sh ? __ldg(w + 4) : 0u;         // never touch a word without needed bytes
+        b0 = __funnelshift_r(a0, a1, sh);
+        b1 = __funnelshift_r(a1, a2, sh);
+        b2 = __funnelshift_r(a2, a3, sh);
+        b3 = __funnelshift_r(a3, a4, sh);
+    }
+};
+
+// FindMatchLength (snappy-internal.h:95-143) over an accessor, 128 bytes per round.
+template <class Src>
+__device__ __forceinline__ uint32_t src_match_len(const Src& src, uint32_t a, uint32_t b,
+                                                  uint32_t end, int lane) {
+    uint32_t n = 0;
+    for (;;) {
+        const uint32_t pb = b + n + (lane << 2);
+        uint32_t m = 0;
+        if (pb < end) {
+            const uint32_t x = src.ld32_upto(a + n + (lane << 2), end) ^ src.ld32_upto(pb, end);
+            m = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
+            m = min(m, end - pb);
+        }
+        const uint32_t bal = __ballot_sync(kFull, m < 4);
+        if (bal) {
+            const int first = __ffs(bal) - 1;
+            return n + (first << 2) + __shfl_sync(kFull, m, first);
+        }
+        n += 128;
+    }
+}
+
+// Serial scan (snappy.cc:587-608) over an accessor; see parse_serial.cuh.
+template <class Src>
+__device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table, int shift,
+                                                uint32_t ip_limit, uint32_t& ip, uint32_t& skip,
+                                                uint32_t& cand) {
+    uint32_t nxt = ip;
+    for (;;) {
+        ip = nxt;
+        const uint32_t step = skip >> 5;
+        skip += step;
+        nxt = ip + step;
+        if (nxt > ip_limit) return false;
+        const uint32_t w = src.ld32(ip);
+        const uint32_t h = hash32(w, shift);
+        cand = table[h];
+        table[h] = (uint16_t)ip;
+        if (src.ld32(cand) == w) return true;
+    }
+}
+
+// ---- ring ---------------------------------------------------------------------------------------
+template <uint32_t R>
+struct alignas(16) PipeShared {
+    uint4 hdr[R];                        // x = L, y = SLOWM, z = inval, w = any_peer (see parse_window.cuh)
+    uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = Sk, w = (4+ml)<<17
+    volatile uint32_t ready[R];          // window index + 1 whose record is complete
+    volatile uint32_t cur_win;           // resolver's current window, kDone when the parse ended
+};
+
+// per-lane "where does the parse go after my copy" (see parse_window.cuh)
+__device__ __forceinline__ uint32_t lane_next(uint32_t pos, uint32_t ek, uint32_t ip_limit,
+                                              uint32_t L, uint32_t SLOWM) {
+    if (pos + ek - (pos & 31u) >= ip_limit) return 256u;    // pos + 4 + ml >= ip_limit
+    if (ek >= 32) return 64u | (ek - 32);
+    const uint32_t m = L & (kFull << ek);
+    if (!m) return 32u;
+    uint32_t v = __ffs(m) - 1;
+    if ((SLOWM >> v) & 1u) v |= 128u;
+    return v;
+}
+
+template <class Src, uint32_t R>
+__device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* table, int shift,
+                                              uint32_t ip_limit, uint32_t nwin, PipeShared<R>* ps,
+                                              uint32_t p, uint32_t P, int lane) {
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t next = p;
+    for (uint32_t idle = 0;;) {
+        const uint32_t cw = ps->cur_win;
+        if (cw == kDone) return;
+        if (next < cw) next = cw + (p + P - cw % P) % P;
+        if (next >= cw + R || next >= nwin) {
+            if (++idle > (1u << 22)) __trap();               // watchdog: never hang the GPU
+            __nanosleep(200);
+            continue;
+        }
+        idle = 0;
+        const uint32_t w = next, si = w % R;
+        const uint32_t pos = (w << 5) + lane;
+        const bool valid = pos < ip_limit;
+        uint32_t d0 = 0, d1 = 0, d2 = 0, d3 = 0;
+        if (valid) src.ld16(pos, d0, d1, d2, d3);
+        const uint32_t h = hash32(d0, shift);
+        const uint32_t T = table[h];                         // speculative: may miss pending inserts
+        const bool peer = (__match_any_sync(kFull, h) & lt) != 0;
+        uint32_t c0 = ~d0, c1 = 0, c2 = 0, c3 = 0;
+        if (valid) src.ld16(T, c0, c1, c2, c3);
+        const bool hit = (c0 == d0);
+        const uint32_t x1 = c1 ^ d1, x2 = c2 ^ d2, x3 = c3 ^ d3;
+        uint32_t ml = 12;
+        if (x3) ml = 8 + ((uint32_t)(__ffs(x3) - 1) >> 3);
+        if (x2) ml = 4 + ((uint32_t)(__ffs(x2) - 1) >> 3);
+        if (x1) ml = (uint32_t)(__ffs(x1) - 1) >> 3;
+        const uint32_t inval = ~__ballot_sync(kFull, valid);
+        const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
+        const uint32_t L = __ballot_sync(kFull, hit || peer) & lanes_below(vpre_end);
+        const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == 12);
+        const uint32_t anyp = __ballot_sync(kFull, peer);
+        const uint32_t ek = lane + 4 + ml;
+        const uint32_t nx = lane_next(pos, ek, ip_limit, L, SLOWM);
+        const uint32_t last_skipped = ek - 1 < 32 ? ek - 1 : 32;
+        const uint32_t Sk = lanes_below(last_skipped) & ~((2u << lane) - 1u);
+        ps->rec[si][lane] = make_uint4(h | (T << 16), nx | (ek << 16), Sk, (4 + ml) << 17);
+        if (lane == 0) ps->hdr[si] = make_uint4(L, SLOWM, inval, anyp);
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) ps->ready[si] = w + 1;
+        next = w + P;
+    }
+}
+
+template <class Src, uint32_t R>
+struct PipeResolver {
+    Src src;
+    uint32_t len, ip_limit;
+    uint16_t* table;
+    PipeShared<R>* ps;
+    int shift, lane;
+    seq_t* seqs;
+    uint32_t nseq;
+    uint32_t next_emit;
+
+    __device__ __forceinline__ void push(uint32_t lit, uint32_t mlen, uint32_t off) {
+        if (lane == 0) seqs[nseq] = seq_pack(lit, mlen, off);
+        ++nseq;
+    }
+
+    __device__ __forceinline__ void run() {
+        const uint32_t lt = (1u << lane) - 1u;
+        uint32_t win = 0, sl = 1, I = 0;
+        int scan0 = 1;
+        for (;;) {
+            // ---- take the producer's record of this window, validate the speculation ----------
+            const uint32_t wbase = win << 5, pos = wbase + lane, si = win % R;
+            for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
+                if (spins > (1u << 24)) __trap();            // watchdog: never hang the GPU
+            __syncwarp();
+            const uint4 rec = ps->rec[si][lane];
+            const uint4 hdr = ps->hdr[si];
+            const uint32_t h = rec.x & 0xffffu;
+            const uint32_t T = table[h];                     // exact: earlier windows are committed
+            uint32_t L = hdr.x, SLOWM = hdr.y, nxek = rec.y;
+            const uint32_t inval = hdr.z, Sk = rec.z;
+            const bool any_peer = hdr.w != 0;
+            const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
+            const uint32_t stale = __ballot_sync(kFull, T != (rec.x >> 16)) & lanes_below(vpre_end);
+            if (stale) {       // those lanes' compare/extension are void: evaluate them if reached
+                L |= stale;
+                SLOWM |= stale;
+                nxek = (nxek & 0xffff0000u) | lane_next(pos, nxek >> 16, ip_limit, L, SLOWM);
+            }
+            // ---- sequential part -------------------------------------------------------------------
+            uint32_t nwin_next = kDone;
+            bool done_window = false;
+            while (!done_window) {
+                const uint32_t vend0 = scan0 < 0 ? (uint32_t)(scan0 + 32) : 32u;
+                const uint32_t m0 = L & lanes_from(sl) & lanes_below(vend0);
+                uint32_t f = 32, chosen = 0, cur_emit = next_emit, mylit = 0;
+                if (m0) { f = __ffs(m0) - 1; if ((SLOWM >> f) & 1u) f |= 128u; }
+                while (f < 32) {                              // one shuffle per copy
+                    chosen |= 1u << f;
+                    if ((uint32_t)lane == f) mylit = pos - cur_emit;
+                    const uint32_t v = __shfl_sync(kFull, nxek, f);
+                    cur_emit = wbase + (v >> 16);
+                    f = v & 0x1ffu;
+                }
+                const uint32_t SK = __reduce_or_sync(kFull, ((chosen >> lane) & 1u) ? Sk : 0u);
+                uint32_t e_last = 0;
+                if (chosen) {
+                    if ((chosen >> lane) & 1u) {
+                        const uint2 q = make_uint2(rec.w | mylit, (pos - T) << 1);
+                        *reinterpret_cast<uint2*>(seqs + nseq + __popc(chosen & lt)) = q;
+                    }
+                    nseq += __popc(chosen);
+                    next_emit = cur_emit;
+                    e_last = cur_emit - wbase;
+                    scan0 = (int)e_last + 1;
+                }
+                uint32_t ip = 0;
+                bool jump = false, e32 = false;        // e32: the copy ended exactly at the window end
+                if (f == 32) {
+                    const uint32_t vend = chosen ? 32u : vend0;
+                    const uint32_t upto = vend < vpre_end ? vend : vpre_end;
+                    I |= lanes_from(sl) & lanes_below(upto) & ~SK;
+                    if (vpre_end <= vend && inval) return;
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    if (vend < 32) {
+                        uint32_t skip = 64, cand;
+                        ip = wbase + vend;
+                        if (!src_serial_scan(src, table, shift, ip_limit, ip, skip, cand)) return;
+                        const uint32_t matched = 4 + src_match_len(src, cand + 4, ip + 4, len, lane);
+                        push(ip - next_emit, matched, ip - cand);
+                        ip += matched;
+                        next_emit = ip;
+                        if (ip >= ip_limit) return;
+                        jump = true;
+                    } else {
+                        nwin_next = win + 1; sl = 0; scan0 -= 32; I = 0;
+                    }
+                    done_window = true;
+                } else if (f & 256u) {
+                    return;
+                } else if (f & 64u) {
+                    I |= lanes_from(sl) & ~SK;
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    ip = next_emit;
+                    jump = true;
+                    e32 = (e_last == 32);
+                    done_window = true;
+                } else {
+                    const uint32_t fs = f & 31u;
+                    I |= lanes_from(sl) & lanes_below(fs) & ~SK;
+                    const uint32_t sameh = __ballot_sync(kFull, h == __shfl_sync(kFull, h, fs));
+                    const uint32_t pk = sameh & I & lanes_below(fs);
+                    const uint32_t cand = pk ? wbase + (31u - __clz(pk)) : __shfl_sync(kFull, T, fs);
+                    const uint32_t p = wbase + fs;
+                    I |= 1u << fs;
+                    if (src.ld32(cand) != src.ld32(p)) { sl = fs + 1; continue; }
+                    const uint32_t matched = 4 + src_match_len(src, cand + 4, p + 4, len, lane);
+                    push(p - next_emit, matched, p - cand);
+                    ip = p + matched;
+                    next_emit = ip;
+                    if (ip >= ip_limit) return;
+                    const uint32_t e = ip - wbase;
+                    if (e <= 32) I |= 1u << (e - 1);
+                    if (e < 32) { sl = e; scan0 = (int)e + 1; continue; }
+                    window_commit(table, h, pos, I, any_peer, lane);
+                    jump = true;
+                    e32 = (e == 32);
+                    done_window = true;
+                }
+                if (jump) {                                   // continue at the window holding ip-1
+                    if (e32) { nwin_next = win + 1; sl = 0; scan0 = 1; I = 0; }   // ip-1 was lane 31: committed above
+                    else {
+                        const uint32_t a = (ip - 1) & 31u;  // insert ip-1 (:649-651) from its own window
+                        nwin_next = (ip - 1) >> 5; I = 1u << a; sl = a + 1; scan0 = (int)a + 2;
+                    }
+                }
+            }
+            win = nwin_next;
+            if (lane == 0) ps->cur_win = win;
+        }
+    }
+};
+
+}  // namespace sb
