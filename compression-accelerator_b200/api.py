@@ -15,7 +15,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsnappy_b200.so")
+LIB_PATH = os.environ.get("SNAPPY_B200_LIB") or os.path.join(_HERE, "libsnappy_b200.so")   # override: A/B builds
 
 EXACT, FAST = 0, 1
 _MODES = {"exact": EXACT, "fast": FAST, "exact_serial": 2, "exact_window": 3, "exact_pipe_smem": 4, EXACT: EXACT, FAST: FAST, 2: 2, 3: 3, 4: 4}
@@ -56,6 +56,7 @@ SYMBOLS = {
     "snappy_b200_launch_count": (C.c_ulonglong, [C.c_void_p]),
     "snappy_b200_last_kernel_ms": (C.c_float, [C.c_void_p]),
     "snappy_b200_stage_ms": (C.c_float, [C.c_void_p, C.c_int]),
+    "snappy_b200_debug_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "snappy_b200_rocc_compress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
     "snappy_b200_rocc_uncompress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
 }
@@ -79,6 +80,13 @@ def lib():
 def _check(status):
     if status != OK:
         raise SnappyB200Error(status, lib().snappy_b200_last_error().decode())
+
+
+def debug_stats(reset=True):
+    """Diagnostics counters of the pipelined parser (zeros unless built with SNAPPY_B200_STATS)."""
+    buf = (C.c_ulonglong * 16)()
+    lib().snappy_b200_debug_stats(buf, 1 if reset else 0)
+    return list(buf)
 
 
 def max_compressed_length(n: int) -> int:

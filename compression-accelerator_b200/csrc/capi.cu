@@ -209,6 +209,10 @@ unsigned long long snappy_b200_launch_count(snappy_b200_ctx* c) { return c ? c->
 
 float snappy_b200_last_kernel_ms(snappy_b200_ctx* c) { return c ? c->last_ms : 0.f; }
 
+int snappy_b200_debug_stats(unsigned long long* out16, int reset) {
+    return sb::read_stats(out16, reset != 0) == cudaSuccess ? 0 : 1;
+}
+
 float snappy_b200_stage_ms(snappy_b200_ctx* c, int stage) {
     if (!c || !c->staged) return 0.f;
     float ms = 0.f;

@@ -79,9 +79,18 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
 // kGlobal = false: fragment staged in shared memory by TMA (2 fragments per SM).
 // kGlobal = true : producers gather the input from global memory; shared memory holds only the
 //                  table and the ring (up to 6 fragments per SM).
+#ifdef SNAPPY_B200_STATS
+__device__ unsigned long long g_stats[16];
+#endif
 template <bool kGlobal> struct PipeCfg;
-template <> struct PipeCfg<false> { static constexpr uint32_t P = 2, R = 8; };
-template <> struct PipeCfg<true>  { static constexpr uint32_t P = 3, R = 6; };
+#ifndef SB_PIPE_P
+#define SB_PIPE_P 4
+#endif
+#ifndef SB_PIPE_LEAD
+#define SB_PIPE_LEAD 3
+#endif
+template <> struct PipeCfg<false> { static constexpr uint32_t P = 2, R = 8, LEAD = 3; };
+template <> struct PipeCfg<true>  { static constexpr uint32_t P = SB_PIPE_P, R = 8, LEAD = SB_PIPE_LEAD; };
 
 template <bool kGlobal>
 __host__ __device__ inline uint32_t pipe_smem_bytes(uint32_t job_len) {
@@ -125,7 +134,7 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
             for (uint32_t i = len + tid; i < padded; i += NT) s_in[i] = 0;
         }
         if (tid < R) ps->ready[tid] = 0;
-        if (tid == 0) ps->cur_win = 0;
+        if (tid == 0) { ps->cur_win = 0; mbar_init(&ps->bar, 1); }
     }
     __syncthreads();
     if (bulk) mbar_wait(bar, 0);
@@ -133,6 +142,9 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
     typedef typename std::conditional<kGlobal, GlobalSrc, SmemSrc>::type Src;
     Src in_src;
     if constexpr (kGlobal) in_src.g = src; else in_src.s = s_in;
+#ifdef SNAPPY_B200_STATS
+    const long long t_start = clock64();
+#endif
     const int shift = 32 - (31 - __clz(entries));
     // spread the resolver warps of co-resident CTAs over the SM's four schedulers
     const uint32_t rwarp = (blockIdx.x / 148u) % (1 + P);
@@ -148,12 +160,23 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
             pr.run();
         }
         __syncwarp();
-        if (lane == 0) ps->cur_win = kDone;
+        if (lane == 0) { ps->cur_win = kDone; mbar_arrive(&ps->bar); }
         if (pr.next_emit < len) pr.push(len - pr.next_emit, 0, 0);
         if (lane == 0) p.nseq[job] = pr.nseq;
+#ifdef SNAPPY_B200_STATS
+        if (lane == 0) {
+            atomicAdd(&g_stats[0], 1ull); atomicAdd(&g_stats[1], (unsigned long long)(clock64() - t_start));
+            atomicAdd(&g_stats[2], pr.st_wait); atomicAdd(&g_stats[3], (unsigned long long)pr.st_win);
+            atomicAdd(&g_stats[4], (unsigned long long)pr.st_stale); atomicAdd(&g_stats[5], (unsigned long long)pr.st_nslow);
+            atomicAdd(&g_stats[6], pr.st_slow); atomicAdd(&g_stats[7], (unsigned long long)pr.st_serial);
+            atomicAdd(&g_stats[8], (unsigned long long)pr.st_slowhit); atomicAdd(&g_stats[9], (unsigned long long)pr.nseq);
+            atomicAdd(&g_stats[12], pr.st_pa); atomicAdd(&g_stats[13], pr.st_pb); atomicAdd(&g_stats[14], pr.st_pc);
+            atomicAdd(&g_stats[10], (unsigned long long)pr.st_cstale); atomicAdd(&g_stats[11], (unsigned long long)pr.st_cpeer);
+        }
+#endif
     } else if (len >= kMargin) {
         const uint32_t pidx = wid > rwarp ? wid - 1 : wid;
-        pipe_producer<Src, R>(in_src, table, shift, len - kMargin, (len + 31) >> 5, ps, pidx, P, (int)lane);
+        pipe_producer<Src, R, PipeCfg<kGlobal>::LEAD>(in_src, table, shift, len, (len + 31) >> 5, ps, pidx, P, (int)lane);
     }
 }
 
@@ -227,6 +250,18 @@ cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStr
 }
 
 // ---- launchers ----------------------------------------------------------------------------------
+cudaError_t read_stats(unsigned long long* out16, bool reset) {
+#ifdef SNAPPY_B200_STATS
+    cudaError_t e = cudaMemcpyFromSymbol(out16, g_stats, 16 * sizeof(unsigned long long));
+    if (e == cudaSuccess && reset) { unsigned long long z[16] = {0}; e = cudaMemcpyToSymbol(g_stats, z, sizeof z); }
+    return e;
+#else
+    for (int i = 0; i < 16; ++i) out16[i] = 0;
+    (void)reset;
+    return cudaSuccess;
+#endif
+}
+
 cudaError_t kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)parse_smem_bytes(kBlock));
@@ -245,7 +280,7 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
                          unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
     if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
-    else if (mode == 0)
+    else if (mode == 0 && p.job_len > 16384)   // small jobs fit many per SM: the single-warp parser wins
         parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
     else if (mode == 4)
         parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);

@@ -57,6 +57,9 @@ cudaError_t launch_scan(const uint32_t* sizes, uint32_t n_frag, unsigned long lo
 // Debug: validate every job's sequence list (lengths add up, offsets in range).
 cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStream_t st);
 
+// Diagnostics counters of the pipelined parser (all zero unless built with -DSNAPPY_B200_STATS).
+cudaError_t read_stats(unsigned long long* out16, bool reset);
+
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 
 }  // namespace sb

@@ -108,20 +108,45 @@ __device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table,
     }
 }
 
+// Slow-path probe of position p against candidate cand in ONE round trip: lane 0 compares the
+// 4-byte words (snappy.cc:607), lanes 1..31 the following 124 bytes (FindMatchLength).  Returns 0
+// when the probe misses, else the match length (>= 4).
+template <class Src>
+__device__ __forceinline__ uint32_t probe_and_extend(const Src& src, uint32_t cand, uint32_t p,
+                                                     uint32_t end, int lane) {
+    const uint32_t pb = p + (lane << 2);
+    uint32_t m = 0;
+    if (pb < end) {
+        const uint32_t x = src.ld32_upto(cand + (lane << 2), end) ^ src.ld32_upto(pb, end);
+        m = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
+        m = min(m, end - pb);
+    }
+    const uint32_t bal = __ballot_sync(kFull, m < 4);
+    if (bal & 1u) return 0;
+    if (bal) {
+        const int first = __ffs(bal) - 1;
+        return (first << 2) + __shfl_sync(kFull, m, first);
+    }
+    return 128 + src_match_len(src, cand + 128, p + 128, end, lane);
+}
+
+constexpr uint32_t kLongMatch = 127;     // pre-extension gave up: evaluate exactly when reached
+
 // ---- ring ---------------------------------------------------------------------------------------
 template <uint32_t R>
 struct alignas(16) PipeShared {
     uint4 hdr[R];                        // x = L, y = SLOWM, z = inval, w = any_peer (see parse_window.cuh)
-    uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = Sk, w = (4+ml)<<17
+    uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = ph (lanes with my hash), w = (4+ml)<<17 | peer<<31
     volatile uint32_t ready[R];          // window index + 1 whose record is complete
     volatile uint32_t cur_win;           // resolver's current window, kDone when the parse ended
+    uint64_t bar;                        // mbarrier (count 1): the resolver arrives whenever cur_win moves
 };
 
 // per-lane "where does the parse go after my copy" (see parse_window.cuh)
 __device__ __forceinline__ uint32_t lane_next(uint32_t pos, uint32_t ek, uint32_t ip_limit,
                                               uint32_t L, uint32_t SLOWM) {
     if (pos + ek - (pos & 31u) >= ip_limit) return 256u;    // pos + 4 + ml >= ip_limit
-    if (ek >= 32) return 64u | (ek - 32);
+    if (ek >= 32) return 64u;                                // my copy leaves the window
     const uint32_t m = L & (kFull << ek);
     if (!m) return 32u;
     uint32_t v = __ffs(m) - 1;
@@ -129,19 +154,23 @@ __device__ __forceinline__ uint32_t lane_next(uint32_t pos, uint32_t ek, uint32_
     return v;
 }
 
-template <class Src, uint32_t R>
+template <class Src, uint32_t R, uint32_t LEAD>
 __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* table, int shift,
-                                              uint32_t ip_limit, uint32_t nwin, PipeShared<R>* ps,
+                                              uint32_t len, uint32_t nwin, PipeShared<R>* ps,
                                               uint32_t p, uint32_t P, int lane) {
+    static_assert(LEAD <= R, "producers may not run ahead of the ring");
+    const uint32_t ip_limit = len - kMargin;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t next = p;
+    uint32_t next = p, parity = 0;
     for (uint32_t idle = 0;;) {
         const uint32_t cw = ps->cur_win;
         if (cw == kDone) return;
         if (next < cw) next = cw + (p + P - cw % P) % P;
-        if (next >= cw + R || next >= nwin) {
-            if (++idle > (1u << 22)) __trap();               // watchdog: never hang the GPU
-            __nanosleep(200);
+        if (next >= cw + LEAD || next >= nwin) {
+            // far enough ahead (or nothing left): sleep in hardware until the resolver moves on.  The
+            // parity is only a belief; a completed phase returns at once and flips it.
+            if (mbar_try_wait(&ps->bar, parity)) parity ^= 1u;
+            if (++idle > (1u << 24)) __trap();               // watchdog: never hang the GPU
             continue;
         }
         idle = 0;
@@ -152,7 +181,6 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
         if (valid) src.ld16(pos, d0, d1, d2, d3);
         const uint32_t h = hash32(d0, shift);
         const uint32_t T = table[h];                         // speculative: may miss pending inserts
-        const bool peer = (__match_any_sync(kFull, h) & lt) != 0;
         uint32_t c0 = ~d0, c1 = 0, c2 = 0, c3 = 0;
         if (valid) src.ld16(T, c0, c1, c2, c3);
         const bool hit = (c0 == d0);
@@ -161,16 +189,33 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
         if (x3) ml = 8 + ((uint32_t)(__ffs(x3) - 1) >> 3);
         if (x2) ml = 4 + ((uint32_t)(__ffs(x2) - 1) >> 3);
         if (x1) ml = (uint32_t)(__ffs(x1) - 1) >> 3;
+        if (hit && ml == 12) {                               // keep extending, 16 bytes a step
+            ml = kLongMatch;
+            for (uint32_t o = 16; o < 80 && pos + o + 16 <= len; o += 16) {
+                uint32_t e0, e1, e2, e3, g0, g1, g2, g3;
+                src.ld16(pos + o, e0, e1, e2, e3);
+                src.ld16(T + o, g0, g1, g2, g3);
+                const uint32_t y0 = e0 ^ g0, y1 = e1 ^ g1, y2 = e2 ^ g2, y3 = e3 ^ g3;
+                if (y0 | y1 | y2 | y3) {
+                    uint32_t q = 12 + ((uint32_t)(__ffs(y3) - 1) >> 3);
+                    if (y2) q = 8 + ((uint32_t)(__ffs(y2) - 1) >> 3);
+                    if (y1) q = 4 + ((uint32_t)(__ffs(y1) - 1) >> 3);
+                    if (y0) q = (uint32_t)(__ffs(y0) - 1) >> 3;
+                    ml = o - 4 + q;
+                    break;
+                }
+            }
+        }
+        const uint32_t ph = __match_any_sync(kFull, h);
+        const bool peer = (ph & lt) != 0;
         const uint32_t inval = ~__ballot_sync(kFull, valid);
         const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
         const uint32_t L = __ballot_sync(kFull, hit || peer) & lanes_below(vpre_end);
-        const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == 12);
+        const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == kLongMatch);
         const uint32_t anyp = __ballot_sync(kFull, peer);
-        const uint32_t ek = lane + 4 + ml;
+        const uint32_t ek = lane + 4 + (ml == kLongMatch ? 12u : ml);
         const uint32_t nx = lane_next(pos, ek, ip_limit, L, SLOWM);
-        const uint32_t last_skipped = ek - 1 < 32 ? ek - 1 : 32;
-        const uint32_t Sk = lanes_below(last_skipped) & ~((2u << lane) - 1u);
-        ps->rec[si][lane] = make_uint4(h | (T << 16), nx | (ek << 16), Sk, (4 + ml) << 17);
+        ps->rec[si][lane] = make_uint4(h | (T << 16), nx | (ek << 16), ph, ((ek - lane) << 17) | ((uint32_t)peer << 31));
         if (lane == 0) ps->hdr[si] = make_uint4(L, SLOWM, inval, anyp);
         __threadfence_block();
         __syncwarp();
@@ -189,6 +234,16 @@ struct PipeResolver {
     seq_t* seqs;
     uint32_t nseq;
     uint32_t next_emit;
+    // diagnostics (SNAPPY_B200_STATS builds only): windows, wait cycles, stale windows, slow evaluations, ...
+    unsigned long long st_wait = 0, st_slow = 0, st_pa = 0, st_pb = 0, st_pc = 0;
+    uint32_t st_win = 0, st_stale = 0, st_nslow = 0, st_serial = 0, st_slowhit = 0, st_cstale = 0, st_cpeer = 0;
+
+    // Write the window's pending inserts: per hash slot the highest inserted lane wins (serial order).
+    __device__ __forceinline__ void commit(uint16_t* tbl, uint32_t h, uint32_t pos, uint32_t I, uint32_t ph) {
+        const uint32_t gt = ~((2u << lane) - 1u);
+        if (((I >> lane) & 1u) && (ph & I & gt) == 0) tbl[h] = (uint16_t)pos;
+        __syncwarp();
+    }
 
     __device__ __forceinline__ void push(uint32_t lit, uint32_t mlen, uint32_t off) {
         if (lane == 0) seqs[nseq] = seq_pack(lit, mlen, off);
@@ -202,23 +257,34 @@ struct PipeResolver {
         for (;;) {
             // ---- take the producer's record of this window, validate the speculation ----------
             const uint32_t wbase = win << 5, pos = wbase + lane, si = win % R;
+#ifdef SNAPPY_B200_STATS
+            const long long t0 = clock64();
+#endif
             for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
                 if (spins > (1u << 24)) __trap();            // watchdog: never hang the GPU
+#ifdef SNAPPY_B200_STATS
+            st_wait += clock64() - t0; ++st_win;
+#endif
             __syncwarp();
             const uint4 rec = ps->rec[si][lane];
             const uint4 hdr = ps->hdr[si];
             const uint32_t h = rec.x & 0xffffu;
             const uint32_t T = table[h];                     // exact: earlier windows are committed
             uint32_t L = hdr.x, SLOWM = hdr.y, nxek = rec.y;
-            const uint32_t inval = hdr.z, Sk = rec.z;
-            const bool any_peer = hdr.w != 0;
+            const uint32_t inval = hdr.z, ph = rec.z;
             const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
             const uint32_t stale = __ballot_sync(kFull, T != (rec.x >> 16)) & lanes_below(vpre_end);
+#ifdef SNAPPY_B200_STATS
+            if (stale) ++st_stale;
+#endif
             if (stale) {       // those lanes' compare/extension are void: evaluate them if reached
                 L |= stale;
                 SLOWM |= stale;
                 nxek = (nxek & 0xffff0000u) | lane_next(pos, nxek >> 16, ip_limit, L, SLOWM);
             }
+#ifdef SNAPPY_B200_STATS
+            const long long t_a = clock64(); st_pa += t_a - t0;
+#endif
             // ---- sequential part -------------------------------------------------------------------
             uint32_t nwin_next = kDone;
             bool done_window = false;
@@ -227,6 +293,9 @@ struct PipeResolver {
                 const uint32_t m0 = L & lanes_from(sl) & lanes_below(vend0);
                 uint32_t f = 32, chosen = 0, cur_emit = next_emit, mylit = 0;
                 if (m0) { f = __ffs(m0) - 1; if ((SLOWM >> f) & 1u) f |= 128u; }
+#ifdef SNAPPY_B200_STATS
+                const long long t_c0 = clock64();
+#endif
                 while (f < 32) {                              // one shuffle per copy
                     chosen |= 1u << f;
                     if ((uint32_t)lane == f) mylit = pos - cur_emit;
@@ -234,11 +303,17 @@ struct PipeResolver {
                     cur_emit = wbase + (v >> 16);
                     f = v & 0x1ffu;
                 }
+#ifdef SNAPPY_B200_STATS
+                const long long t_b0 = clock64(); st_pc += t_b0 - t_c0;
+#endif
+                // lanes strictly inside a taken copy (lane+1 .. ek-2) are not inserted
+                const uint32_t ek = nxek >> 16;
+                const uint32_t Sk = lanes_below(ek - 1 < 32 ? ek - 1 : 32) & ~((2u << lane) - 1u);
                 const uint32_t SK = __reduce_or_sync(kFull, ((chosen >> lane) & 1u) ? Sk : 0u);
                 uint32_t e_last = 0;
                 if (chosen) {
                     if ((chosen >> lane) & 1u) {
-                        const uint2 q = make_uint2(rec.w | mylit, (pos - T) << 1);
+                        const uint2 q = make_uint2((rec.w & 0x7fffffffu) | mylit, (pos - T) << 1);
                         *reinterpret_cast<uint2*>(seqs + nseq + __popc(chosen & lt)) = q;
                     }
                     nseq += __popc(chosen);
@@ -253,9 +328,12 @@ struct PipeResolver {
                     const uint32_t upto = vend < vpre_end ? vend : vpre_end;
                     I |= lanes_from(sl) & lanes_below(upto) & ~SK;
                     if (vpre_end <= vend && inval) return;
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(table, h, pos, I, ph);
                     if (vend < 32) {
                         uint32_t skip = 64, cand;
+#ifdef SNAPPY_B200_STATS
+                        ++st_serial;
+#endif
                         ip = wbase + vend;
                         if (!src_serial_scan(src, table, shift, ip_limit, ip, skip, cand)) return;
                         const uint32_t matched = 4 + src_match_len(src, cand + 4, ip + 4, len, lane);
@@ -272,21 +350,27 @@ struct PipeResolver {
                     return;
                 } else if (f & 64u) {
                     I |= lanes_from(sl) & ~SK;
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(table, h, pos, I, ph);
                     ip = next_emit;
                     jump = true;
                     e32 = (e_last == 32);
                     done_window = true;
                 } else {
                     const uint32_t fs = f & 31u;
+#ifdef SNAPPY_B200_STATS
+                    ++st_nslow; const long long t1 = clock64();
+                    if ((stale >> fs) & 1u) ++st_cstale; else if (__shfl_sync(kFull, rec.w, fs) >> 31) ++st_cpeer;
+#endif
                     I |= lanes_from(sl) & lanes_below(fs) & ~SK;
-                    const uint32_t sameh = __ballot_sync(kFull, h == __shfl_sync(kFull, h, fs));
-                    const uint32_t pk = sameh & I & lanes_below(fs);
+                    const uint32_t pk = __shfl_sync(kFull, ph, fs) & I & lanes_below(fs);   // inserted peers
                     const uint32_t cand = pk ? wbase + (31u - __clz(pk)) : __shfl_sync(kFull, T, fs);
                     const uint32_t p = wbase + fs;
                     I |= 1u << fs;
-                    if (src.ld32(cand) != src.ld32(p)) { sl = fs + 1; continue; }
-                    const uint32_t matched = 4 + src_match_len(src, cand + 4, p + 4, len, lane);
+                    const uint32_t matched = probe_and_extend(src, cand, p, len, lane);
+#ifdef SNAPPY_B200_STATS
+                    st_slow += clock64() - t1; if (matched) ++st_slowhit;
+#endif
+                    if (!matched) { sl = fs + 1; continue; }             // missed probe (:607)
                     push(p - next_emit, matched, p - cand);
                     ip = p + matched;
                     next_emit = ip;
@@ -294,7 +378,7 @@ struct PipeResolver {
                     const uint32_t e = ip - wbase;
                     if (e <= 32) I |= 1u << (e - 1);
                     if (e < 32) { sl = e; scan0 = (int)e + 1; continue; }
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(table, h, pos, I, ph);
                     jump = true;
                     e32 = (e == 32);
                     done_window = true;
@@ -307,8 +391,11 @@ struct PipeResolver {
                     }
                 }
             }
+#ifdef SNAPPY_B200_STATS
+            st_pb += clock64() - t_a;
+#endif
             win = nwin_next;
-            if (lane == 0) ps->cur_win = win;
+            if (lane == 0) { ps->cur_win = win; mbar_arrive(&ps->bar); }
         }
     }
 };

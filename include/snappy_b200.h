@@ -108,6 +108,10 @@ float snappy_b200_last_kernel_ms(snappy_b200_ctx* ctx);
  * after snappy_b200_sync(). */
 float snappy_b200_stage_ms(snappy_b200_ctx* ctx, int stage);
 
+/* Diagnostics: 16 counters of the pipelined parser since the last reset (all zero unless the
+ * library was built with -DSNAPPY_B200_STATS).  Returns 0 on success. */
+int snappy_b200_debug_stats(unsigned long long* out16, int reset);
+
 /* ---- RoCC driver mirror: tests/compression.c:20-27 and :32-39.  Host pointers, blocking.
  * compress returns the compressed length (0 on failure: a valid stream is never empty);
  * uncompress returns 0 on success, non-zero on failure, as the reference documents. */

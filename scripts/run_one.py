@@ -51,6 +51,13 @@ def main():
         tot = int(out_n.item())
         print("%s %s %.1f MiB: parse %.3f ms  gather %.3f ms  %.2f GB/s in, out/in %.4f" % (
             a.data, a.mode, n / 2**20, p, s, n / (p + s) / 1e6, tot / n))
+    st = pkg.debug_stats()
+    if st[0]:
+        f = st[0]
+        print('stats per fragment: cycles %.0f wait %.0f windows %.1f stale %.1f slow %.1f (hits %.1f, cycles %.0f) serial %.2f seqs %.0f slow-by-cause stale %.0f peer %.0f' % (
+            st[1] / f, st[2] / f, st[3] / f, st[4] / f, st[5] / f, st[8] / f, st[6] / f, st[7] / f, st[9] / f, st[10] / f, st[11] / f))
+    if st[0]:
+        print('  phases per window: entry(wait+load+validate) %.0f  sequential %.0f (of which chase %.0f)' % (st[12] / st[3], st[13] / st[3], st[14] / st[3]))
     if a.check:
         import oracle_lib
         chk = oracle_lib.checker()
