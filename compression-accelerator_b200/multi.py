@@ -1,0 +1,137 @@
+"""Multi-GPU Snappy: fragments sharded over the GPUs of one box, one process per GPU.
+
+Snappy's fragments are independent (fresh table and base pointer per 64 KiB block,
+reference tests/snappy/snappy.cc:1013-1061); the only datum that crosses a fragment boundary is
+the running output offset.  So a stream shards with exactly one exchange step:
+
+    rank r compresses fragments [F*r/R, F*(r+1)/R) of the stream, header-less   (local kernels)
+    all_gather of one int64 per rank: the payload sizes                         (NCCL, 8 B/rank)
+    exclusive scan of the sizes -> payload offsets (+ the varint header length)
+    payload of rank r lands at dst + hdr + offset[r] on the root                (NCCL send/recv)
+
+The root writes varint32(N).  The result is byte-identical to the single-GPU stream.  The same
+exchange with hdr = 0 and whole streams per rank builds an "archive" of streams (inputs of 4 GiB
+and more cannot be ONE Snappy stream: the preamble is a varint32, snappy.cc:1006-1007).
+
+torch.distributed is plumbing only; the exchange also runs over gloo with CPU tensors, which is
+how tests/test_multi.py covers it without a GPU.
+"""
+import torch
+import torch.distributed as dist
+
+BLOCK = 65536
+
+
+def fragment_range(n_total: int, rank: int, world: int):
+    """Byte range [lo, hi) of rank's run of whole fragments: fragments [F*r/R, F*(r+1)/R)."""
+    n_frag = (n_total + BLOCK - 1) // BLOCK
+    f_lo = n_frag * rank // world
+    f_hi = n_frag * (rank + 1) // world
+    return min(f_lo * BLOCK, n_total), min(f_hi * BLOCK, n_total)
+
+
+def varint32(n: int) -> bytes:
+    """tests/snappy/snappy-stubs-internal.h:552-578 (host-side copy for the root's header)."""
+    out = bytearray()
+    while n >= 128:
+        out.append((n & 0x7F) | 0x80)
+        n >>= 7
+    out.append(n)
+    return bytes(out)
+
+
+class PayloadExchange:
+    """The exchange step: all_gather(sizes) -> scan -> gather payload on `root`.
+
+    payload / dst are uint8 tensors on the process group's device type (CUDA for NCCL, CPU for
+    gloo).  Every call is collective over `group`."""
+
+    def __init__(self, device, group=None, root: int = 0):
+        self.device, self.group, self.root = device, group, root
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self._sizes = torch.zeros(self.world, dtype=torch.int64, device=device)
+        self._mine = torch.zeros(1, dtype=torch.int64, device=device)
+        self.launch_like_ops = 0          # collectives issued (not kernels of ours)
+
+    def sizes(self, my_size) -> torch.Tensor:
+        """all_gather of one int64 per rank.  my_size: python int or 1-element int64 tensor."""
+        if isinstance(my_size, torch.Tensor):
+            self._mine.copy_(my_size.reshape(1).to(torch.int64))
+        else:
+            self._mine.fill_(int(my_size))
+        dist.all_gather_into_tensor(self._sizes, self._mine, group=self.group)
+        self.launch_like_ops += 1
+        return self._sizes
+
+    def gather(self, payload: torch.Tensor, my_size, dst: torch.Tensor = None, base: int = 0):
+        """Returns (total_len, offsets list).  On the root, dst[base + off[r] : +size[r]] holds rank r's
+        payload afterwards (the root's own payload is copied locally)."""
+        sizes = self.sizes(my_size).tolist()              # host sync: 8 bytes per rank
+        offs, run = [], base
+        for s in sizes:
+            offs.append(run)
+            run += s
+        if self.rank == self.root:
+            if dst is None or dst.numel() < run:
+                raise ValueError("root dst too small: need %d bytes" % run)
+            ops = []
+            for r in range(self.world):
+                if sizes[r] == 0:
+                    continue
+                view = dst[offs[r]:offs[r] + sizes[r]]
+                if r == self.root:
+                    view.copy_(payload[:sizes[r]])
+                else:
+                    ops.append(dist.P2POp(dist.irecv, view, r, group=self.group))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+                self.launch_like_ops += 1
+        elif sizes[self.rank]:
+            ops = [dist.P2POp(dist.isend, payload[:sizes[self.rank]], self.root, group=self.group)]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            self.launch_like_ops += 1
+        return run, offs
+
+
+class ShardedStream:
+    """ONE Snappy stream of n_total bytes (< 2^32) compressed by all ranks of the group.
+
+    compress_fragments(src_shard) -> (payload tensor, size) is the local, header-less compression of
+    a run of whole fragments: on the GPU it is Context.compress_device(..., header=False)."""
+
+    def __init__(self, n_total: int, device, group=None, root: int = 0):
+        if n_total >= 1 << 32:
+            raise ValueError("a Snappy stream holds < 2^32 bytes; use an archive of streams")
+        self.n_total = n_total
+        self.ex = PayloadExchange(device, group, root)
+        self.lo, self.hi = fragment_range(n_total, self.ex.rank, self.ex.world)
+        self.header = varint32(n_total)
+
+    def assemble(self, payload: torch.Tensor, my_size, dst: torch.Tensor = None) -> int:
+        """Collective.  Returns the stream length; on the root dst[:length] is the stream."""
+        hdr = len(self.header)
+        if self.ex.rank == self.ex.root and dst is not None:
+            dst[:hdr].copy_(torch.frombuffer(bytearray(self.header), dtype=torch.uint8))
+        total, _ = self.ex.gather(payload, my_size, dst, base=hdr)
+        return total
+
+
+class ArchiveGather:
+    """Weak-scaling shape of bench.py: every rank compresses its own whole stream; the streams are
+    packed back to back on the root, offsets from the all-gathered sizes."""
+
+    def __init__(self, ctx, device, cap_per_rank: int, group=None, root: int = 0):
+        self.ctx = ctx
+        self.ex = PayloadExchange(device, group, root)
+        self.archive = None
+        if self.ex.rank == root:
+            self.archive = torch.empty(cap_per_rank * self.ex.world, dtype=torch.uint8, device=device)
+        self.offsets = None
+        self.total = 0
+
+    def exchange(self, stream: torch.Tensor, out_n: torch.Tensor) -> int:
+        self.total, self.offsets = self.ex.gather(stream, out_n, self.archive, base=0)
+        return self.total
