@@ -59,6 +59,21 @@ SYMBOLS = {
     "snappy_b200_debug_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "snappy_b200_rocc_compress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
     "snappy_b200_rocc_uncompress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
+    # include/b200_rocc.h: the accelerator's top-level IO (ScratchpadTest.scala:23-51)
+    "b200_rocc_new": (C.c_void_p, [C.c_size_t, C.c_int]),
+    "b200_rocc_free": (None, [C.c_void_p]),
+    "b200_rocc_load_mem": (C.c_long, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64]),
+    "b200_rocc_load_mem_file": (C.c_long, [C.c_void_p, C.c_char_p, C.c_uint64]),
+    "b200_rocc_mem": (C.c_void_p, [C.c_void_p]),
+    "b200_rocc_mem_bytes": (C.c_size_t, [C.c_void_p]),
+    "b200_rocc_poke_cmd": (None, [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_int]),
+    "b200_rocc_step": (None, [C.c_void_p, C.c_uint64]),
+    "b200_rocc_peek_cmd_ready": (C.c_int, [C.c_void_p]),
+    "b200_rocc_peek_busy": (C.c_int, [C.c_void_p]),
+    "b200_rocc_peek_resp_valid": (C.c_int, [C.c_void_p]),
+    "b200_rocc_peek_resp_data": (C.c_uint64, [C.c_void_p]),
+    "b200_rocc_peek_busy_cycles": (C.c_uint64, [C.c_void_p]),
+    "b200_rocc_peek_interrupt": (C.c_int, [C.c_void_p]),
 }
 
 
@@ -234,3 +249,63 @@ def rocc_uncompress(source, compressed_length: int, dest) -> int:
     """uncompress(source, compressed_length, dest) of tests/compression.c:32-39: 0 on success."""
     src = source if isinstance(source, bytes) else _addr(source)
     return int(lib().snappy_b200_rocc_uncompress(src, compressed_length, _addr(dest)))
+
+
+class RoccDevice:
+    """ScratchpadTestModule.io as an object (src/main/scala/example/ScratchpadTest.scala:23-51):
+    ``poke_cmd`` / ``step`` / ``peek_*`` follow the PeekPokeTester calls of
+    src/test/scala/example/Test.scala:17-53; ``load_mem`` is loadMemoryFromFile (:38)."""
+    COMPRESS, UNCOMPRESS, SET_LENGTH = 0, 1, 2          # tests/compression.c:13-15
+
+    def __init__(self, mem_bytes: int = 0, device: int = 0):
+        self._h = lib().b200_rocc_new(mem_bytes, device)
+        if not self._h:
+            raise SnappyB200Error(NO_DEVICE, lib().snappy_b200_last_error().decode() or "b200_rocc_new failed")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200_rocc_free(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def load_mem(self, data: bytes, addr: int = 0) -> int:
+        return lib().b200_rocc_load_mem(self._h, data, len(data), addr)
+
+    def read_mem(self, addr: int, n: int) -> bytes:
+        return C.string_at(lib().b200_rocc_mem(self._h) + addr, n)
+
+    def poke_cmd(self, funct: int, rs1: int = 0, rs2: int = 0, valid: bool = True):
+        lib().b200_rocc_poke_cmd(self._h, funct, rs1, rs2, 1 if valid else 0)
+
+    def step(self, n: int = 1):
+        lib().b200_rocc_step(self._h, n)
+
+    def peek_resp_valid(self) -> int:
+        return lib().b200_rocc_peek_resp_valid(self._h)
+
+    def peek_resp_data(self) -> int:
+        return lib().b200_rocc_peek_resp_data(self._h)
+
+    def peek_busy_cycles(self) -> int:
+        return lib().b200_rocc_peek_busy_cycles(self._h)
+
+    def peek_busy(self) -> int:
+        return lib().b200_rocc_peek_busy(self._h)
+
+    def run_compress(self, length: int):
+        """The tester's whole protocol (Test.scala:27-53) for data preloaded at address 0:
+        returns (busy_cycles, compressed_length, dst_address)."""
+        dst = -(-length // 8) * 8 + 8                      # Test.scala:35
+        c0 = self.peek_busy_cycles()
+        self.poke_cmd(self.SET_LENGTH, length)             # :27-30
+        self.step(1)
+        self.poke_cmd(self.COMPRESS, 0, dst)               # :33-36
+        self.step(1)
+        self.poke_cmd(self.COMPRESS, 0, dst, valid=False)  # :39
+        timeout = 0
+        while not self.peek_resp_valid() and timeout < 50 * max(length, 1):   # :42-47
+            self.step(1)
+            timeout += 1
+        self.step(20)                                      # :50
+        return self.peek_busy_cycles() - c0, self.peek_resp_data(), dst

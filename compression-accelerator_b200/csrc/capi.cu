@@ -7,6 +7,7 @@
 
 #include <mutex>
 #include <new>
+#include <vector>
 
 #include "../../include/snappy_b200.h"
 #include "kernels.h"
@@ -58,6 +59,13 @@ struct snappy_b200_ctx {
     bool staged = false;
     unsigned long long launches = 0;
     float last_ms = 0.f;
+    // chunk pipeline of the host entry: H2D stream, parse streams, D2H stream; per-chunk events;
+    // running stream length mirrored into mapped pinned host words by the scan kernel
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_parse[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_start = nullptr;
+    std::vector<cudaEvent_t> ev_h, ev_p, ev_e;
+    unsigned long long* h_run = nullptr;       // pinned + mapped, kMaxChunks words
+    unsigned long long* h_run_dev = nullptr;   // its device alias
 };
 
 namespace {
@@ -125,6 +133,114 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
+    return SNAPPY_B200_OK;
+}
+
+constexpr size_t kMaxChunks = 1024;
+constexpr size_t kPipeMinBytes = 24u << 20;     // below this one H2D + one D2H is as good as it gets
+
+// Chunk size of the host pipeline: whole fragments; large inputs use 64 MiB (1024 fragments, a
+// little more than one resident wave of the pipelined parser), smaller ones an eighth.
+size_t pipe_chunk_bytes(size_t n) {
+    static const size_t env = [] { const char* e = getenv("SNAPPY_B200_CHUNK_MIB"); return e ? (size_t)atol(e) << 20 : (size_t)0; }();
+    size_t c = env ? env : (n >= (512u << 20) ? (64u << 20) : n / 8);
+    c = (c + sb::kBlock - 1) / sb::kBlock * sb::kBlock;
+    if (c < (4u << 20)) c = 4u << 20;
+    while ((n + c - 1) / c > kMaxChunks) c *= 2;
+    return c;
+}
+
+snappy_b200_status ensure_pipe(snappy_b200_ctx* c, size_t n_chunks) {
+    if (!c->s_h2d) {
+        CU(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+        for (auto& s : c->s_parse) CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&c->ev_start, cudaEventDisableTiming));
+        CU(cudaHostAlloc((void**)&c->h_run, kMaxChunks * sizeof(unsigned long long), cudaHostAllocMapped));
+        CU(cudaHostGetDevicePointer((void**)&c->h_run_dev, c->h_run, 0));
+    }
+    while (c->ev_h.size() < n_chunks) {
+        cudaEvent_t a, b, d;
+        CU(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&d, cudaEventDisableTiming));
+        c->ev_h.push_back(a); c->ev_p.push_back(b); c->ev_e.push_back(d);
+    }
+    return SNAPPY_B200_OK;
+}
+
+// Host entry for large inputs: the stream is cut into chunks of whole fragments and the chunks
+// flow through H2D -> parse -> size/scan/emit -> D2H on separate CUDA streams, so the PCIe copies
+// of chunk k+1 / k-1 overlap the kernels of chunk k, and the parse kernels of neighbouring
+// chunks overlap each other's tails.  Fragment outputs land at their final offsets in one device
+// buffer (the scan carries the running length across chunks), so the bytes are those of the
+// one-shot path.
+snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* src, size_t n,
+                                           uint8_t* dst, size_t dst_cap, size_t* out_n, int mode) {
+    const size_t cap = snappy_b200_max_compressed_length(n);
+    const size_t chunk = pipe_chunk_bytes(n);
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
+    const uint32_t hdr = sb::varint32_len((uint32_t)n);
+    if (ensure_pipe(c, n_chunks) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(c->d_in.reserve(n + 64));
+    CU(c->d_out.reserve(cap + 64));
+    CU(c->seqs.reserve((size_t)n_frag * sb::seq_stride(sb::kBlock) * sizeof(sb::seq_t) + 256));
+    CU(c->nseq.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
+    CU(c->sizes.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
+    CU(c->offsets.reserve((size_t)(n_frag + 1) * sizeof(unsigned long long)));
+    uint8_t* d_in = (uint8_t*)c->d_in.p;
+    uint8_t* d_out = (uint8_t*)c->d_out.p;
+    // nothing of this call may overtake earlier work on the context's stream (shared scratch)
+    CU(cudaEventRecord(c->ev_start, c->stream));
+    CU(cudaStreamWaitEvent(c->s_h2d, c->ev_start, 0));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    for (size_t k = 0; k < n_chunks; ++k) {
+        const size_t lo = k * chunk, len = (n - lo < chunk) ? n - lo : chunk;
+        const uint32_t f0 = (uint32_t)(lo / sb::kBlock);
+        CU(cudaMemcpyAsync(d_in + lo, src + lo, len, cudaMemcpyHostToDevice, c->s_h2d));
+        CU(cudaEventRecord(c->ev_h[k], c->s_h2d));
+        sb::JobParams p;
+        p.in = d_in + lo;
+        p.n_total = len;
+        p.in_stride = sb::kBlock;
+        p.job_len = sb::kBlock;
+        p.n_jobs = (uint32_t)((len + sb::kBlock - 1) / sb::kBlock);
+        p.seqs = (sb::seq_t*)c->seqs.p + (size_t)f0 * sb::seq_stride(sb::kBlock);
+        p.nseq = (uint32_t*)c->nseq.p + f0;
+        p.sizes = (uint32_t*)c->sizes.p + f0;
+        p.with_header = 0;
+        p.out = d_out;
+        p.out_stride = 0;
+        p.offsets = (const unsigned long long*)c->offsets.p + f0;
+        cudaStream_t ps = c->s_parse[k & 3];
+        CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
+        CU(sb::launch_parse(p, mode, ps, &c->launches));
+        CU(cudaEventRecord(c->ev_p[k], ps));
+        CU(cudaStreamWaitEvent(c->stream, c->ev_p[k], 0));
+        CU(sb::launch_size(p, c->stream, &c->launches));
+        CU(sb::launch_scan(p.sizes, p.n_jobs, (unsigned long long*)c->offsets.p + f0, k == 0 ? hdr : 0,
+                           (uint32_t)n, d_out, c->d_total, c->stream, &c->launches,
+                           k == 0 ? nullptr : c->d_total, c->h_run_dev + k));
+        CU(sb::launch_emit(p, c->stream, &c->launches));
+        CU(cudaEventRecord(c->ev_e[k], c->stream));
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+    // drain: as soon as chunk k's elements are in place its byte range goes back to the host
+    size_t done = 0;
+    snappy_b200_status st = SNAPPY_B200_OK;
+    for (size_t k = 0; k < n_chunks; ++k) {
+        CU(cudaEventSynchronize(c->ev_e[k]));
+        const size_t run = (size_t)*(volatile unsigned long long*)(c->h_run + k);
+        if (run > dst_cap) { st = fail(SNAPPY_B200_BUFFER_TOO_SMALL, "stream larger than dst_cap"); break; }
+        if (run > done) CU(cudaMemcpyAsync(dst + done, d_out + done, run - done, cudaMemcpyDeviceToHost, c->s_d2h));
+        done = run;
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaStreamSynchronize(c->s_d2h));
+    if (st != SNAPPY_B200_OK) return st;
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    *out_n = done;
     return SNAPPY_B200_OK;
 }
 
@@ -199,6 +315,14 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (c->evp1) cudaEventDestroy(c->evp1);
     if (c->evp2) cudaEventDestroy(c->evp2);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
+    if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
+    for (auto s_ : c->s_parse) if (s_) cudaStreamDestroy(s_);
+    if (c->ev_start) cudaEventDestroy(c->ev_start);
+    for (auto e_ : c->ev_h) cudaEventDestroy(e_);
+    for (auto e_ : c->ev_p) cudaEventDestroy(e_);
+    for (auto e_ : c->ev_e) cudaEventDestroy(e_);
+    if (c->h_run) cudaFreeHost(c->h_run);
     if (g_default_ctx == c) g_default_ctx = nullptr;
     delete c;
 }
@@ -298,6 +422,8 @@ snappy_b200_status snappy_b200_compress(snappy_b200_ctx* c, const void* src, siz
     if (!c) { snappy_b200_status st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     const size_t cap = snappy_b200_max_compressed_length(n);
+    if (n >= kPipeMinBytes)
+        return compress_host_pipelined(c, (const uint8_t*)src, n, (uint8_t*)dst, dst_cap, out_n, mode);
     CU(c->d_in.reserve(n + 64));
     CU(c->d_out.reserve(cap + 64));
     if (n) CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));

@@ -185,12 +185,14 @@ __global__ void __launch_bounds__(1024) scan_sizes_kernel(const uint32_t* __rest
                                                           uint32_t n, unsigned long long* offsets,
                                                           uint32_t hdr_len, uint32_t n_input,
                                                           uint8_t* dst,
-                                                          unsigned long long* d_total) {
+                                                          unsigned long long* d_total,
+                                                          const unsigned long long* carry_in,
+                                                          unsigned long long* h_mirror) {
     __shared__ unsigned long long warp_sum[32];
     __shared__ unsigned long long carry_s;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) {
-        carry_s = hdr_len;
+        carry_s = hdr_len + (carry_in ? *carry_in : 0ull);   // later chunks continue the running offset
         if (hdr_len) put_varint32(dst, n_input);             // snappy.cc:1006-1009
     }
     __syncthreads();
@@ -218,7 +220,10 @@ __global__ void __launch_bounds__(1024) scan_sizes_kernel(const uint32_t* __rest
         if (tid == 1023) carry_s = excl + v;
         __syncthreads();
     }
-    if (tid == 0) *d_total = carry_s;
+    if (tid == 0) {
+        *d_total = carry_s;
+        if (h_mirror) { *h_mirror = carry_s; __threadfence_system(); }   // mapped pinned host word
+    }
 }
 
 // ---- debug self-check of the sequence lists (SNAPPY_B200_DEBUG=1) -----------------------------
@@ -306,8 +311,10 @@ cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long*
 cudaError_t launch_scan(const uint32_t* sizes, uint32_t n_frag, unsigned long long* offsets,
                         uint32_t hdr_len, uint32_t n_input, uint8_t* dst,
                         unsigned long long* d_total, cudaStream_t st,
-                        unsigned long long* launches) {
-    scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, n_frag, offsets, hdr_len, n_input, dst, d_total);
+                        unsigned long long* launches, const unsigned long long* carry_in,
+                        unsigned long long* h_mirror) {
+    scan_sizes_kernel<<<1, 1024, 0, st>>>(sizes, n_frag, offsets, hdr_len, n_input, dst, d_total,
+                                          carry_in, h_mirror);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

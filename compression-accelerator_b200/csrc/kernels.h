@@ -48,11 +48,14 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 
-// Exclusive scan of sizes[0..n_frag) (+hdr_len) into offsets (uint64), total stream length into
-// *d_total; writes varint32(n_input) at dst when hdr_len > 0.
+// Exclusive scan of sizes[0..n_frag) (+hdr_len, + *carry_in when given) into offsets (uint64),
+// running stream length into *d_total (and into *h_mirror, a mapped pinned host word, when
+// given); writes varint32(n_input) at dst when hdr_len > 0.
 cudaError_t launch_scan(const uint32_t* sizes, uint32_t n_frag, unsigned long long* offsets,
                         uint32_t hdr_len, uint32_t n_input, uint8_t* dst,
-                        unsigned long long* d_total, cudaStream_t st, unsigned long long* launches);
+                        unsigned long long* d_total, cudaStream_t st, unsigned long long* launches,
+                        const unsigned long long* carry_in = nullptr,
+                        unsigned long long* h_mirror = nullptr);
 
 // Debug: validate every job's sequence list (lengths add up, offsets in range).
 cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStream_t st);

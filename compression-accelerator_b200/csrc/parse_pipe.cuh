@@ -24,6 +24,9 @@
 namespace sb {
 
 constexpr uint32_t kDone = 0xffffffffu;
+#ifndef SB_PIPE_SLEEP
+#define SB_PIPE_SLEEP 100
+#endif
 
 // ---- input accessors ------------------------------------------------------------------------
 struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
@@ -170,6 +173,9 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
             // far enough ahead (or nothing left): sleep in hardware until the resolver moves on.  The
             // parity is only a belief; a completed phase returns at once and flips it.
             if (mbar_try_wait(&ps->bar, parity)) parity ^= 1u;
+#if SB_PIPE_SLEEP > 0
+            else __nanosleep(SB_PIPE_SLEEP);                 // try_wait times out quickly: do not burn issue slots
+#endif
             if (++idle > (1u << 24)) __trap();               // watchdog: never hang the GPU
             continue;
         }

@@ -145,3 +145,39 @@ def test_large_stream_property(ctx, oracle):
     # first 4 MiB compared bytewise with the oracle's stream of the same prefix fragments
     pre = oracle.compress(host[:4 << 20].tobytes())
     assert bytes(comp[5:5 + len(pre) - 4]) == pre[4:]
+
+
+def test_host_entry_chunk_pipeline(ctx, oracle):
+    """Inputs of 24 MiB and more go through the chunked H2D/parse/emit/D2H pipeline of the host
+    entry; the stream must still be the oracle's, byte for byte (odd length, ragged last chunk)."""
+    n = (70 << 20) + 12345
+    host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)
+    host[5 << 20:(5 << 20) + (3 << 20)] = corpus.random_ascii(3 << 20, 3)      # a literal-heavy stretch
+    host[(40 << 20) + 77:(40 << 20) + 77 + (2 << 20)] = 97                      # and a long run
+    data = host.tobytes()
+    comp = ctx.compress(data)
+    want = oracle.compress(data)
+    assert len(comp) == len(want)
+    assert comp == want
+
+
+def test_rocc_device_protocol(pkg, oracle):
+    """The Scala tester's poke/step/peek protocol (Test.scala:17-53) over the C-ABI device object,
+    for the benchmark size sweep; prints the `type;length;cycles;compressed-length` rows of
+    benchmark/hw_results.csv and checks stream bytes, which the reference harness never did."""
+    dev = pkg.RoccDevice()
+    try:
+        rows = []
+        for kind in ("random", "real", "repeating"):
+            for n in corpus.SWEEP_SIZES:
+                data = corpus.benchmark_file(kind, n)
+                dev.load_mem(data, 0)
+                cycles, clen, dst = dev.run_compress(n)
+                want = oracle.compress(data)
+                assert clen == len(want), (kind, n)
+                assert dev.read_mem(dst, clen) == want, (kind, n)
+                assert clen == MAN["sweep"]["%s-%d" % (kind, n)]["compressed_n"]
+                rows.append("%s;%d;%d;%d" % (kind, n, cycles, clen))
+        assert len(rows) == 36
+    finally:
+        dev.close()

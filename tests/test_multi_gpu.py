@@ -1,0 +1,72 @@
+"""Sharded single stream over NCCL on >= 2 GPUs: every rank compresses its run of whole fragments
+with the CUDA path (header-less), the exchange step assembles the stream on rank 0, and the
+result must be byte-identical to the oracle's one-shot stream.  Skipped on a 1-GPU box."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import corpus
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n_total, q):
+    for p in (HERE, ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import __graft_entry__ as g
+    import oracle_lib
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        pkg = g.load_package()
+        from compression_accelerator_b200 import multi
+        ctx = pkg.Context(rank)
+        host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n_total)
+        sh = multi.ShardedStream(n_total, dev)
+        shard = torch.from_numpy(host[sh.lo:sh.hi].copy()).to(dev)
+        stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+        payload, size = ctx.compress_device(shard, header=False)
+        dst = torch.zeros(pkg.max_compressed_length(n_total) + 16, dtype=torch.uint8, device=dev) if rank == 0 else None
+        with torch.cuda.stream(stream):
+            total = sh.assemble(payload, size, dst)
+        torch.cuda.synchronize()
+        if rank == 0:
+            want = oracle_lib.checker().compress(host.tobytes())
+            q.put((total == len(want), bytes(dst[:total].cpu().numpy()) == want, total))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_total", [65536 * 37 + 4321, 1 << 26])
+def test_sharded_stream_nccl(n_total):
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    len_ok, bytes_ok, total = q.get(timeout=5)
+    assert len_ok and bytes_ok, (n_total, total)
