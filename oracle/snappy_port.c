@@ -247,3 +247,65 @@ int port_uncompress(const uint8_t *src, size_t n, uint8_t *dst, size_t dst_cap, 
     *out_len = op;
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Model of libsnappy_b200's FAST mode (SNAPPY_B200_FAST) -- NOT a restatement of the reference.
+ * The fast mode is a parallel parse whose bytes may differ from the reference's; it is fully
+ * deterministic, and this sequential model defines it so that tests can pin the CUDA kernel's
+ * stream byte for byte (and measure its ratio against the reference within the stated 2 %).
+ *
+ *   candidates  the fragment is cut into aligned windows of 32 positions.  Every position p with
+ *               p + 4 <= len is looked up in the same uint16 table / hash as the reference
+ *               (snappy.cc:91-97, :445-456) as it stands after the PREVIOUS window, then all the
+ *               window's positions are inserted (ascending, so the highest position of a slot
+ *               stays): cand(p) = most recent position with p's hash in an earlier window (0 if none).
+ *               Exception: if the 4 bytes at p - 1 equal the 4 bytes at p (a run), cand(p) = p - 1.
+ *   hit(p)      p > 0 and the 4 bytes at cand(p) equal those at p; mlen(p) = common prefix,
+ *               capped at 1024 and at len - p; long copies are split by EmitCopy (snappy.cc:402-431).
+ *   parse       greedy: at p, if hit(p) emit literal [next_emit, p) + copy(p - cand, mlen) and
+ *               continue at p + mlen, else p + 1.  No skip heuristic, no end margin.
+ */
+size_t port_fast_compress_fragment(const uint8_t *in, uint32_t len, uint8_t *out,
+                                   uint16_t *table, uint32_t entries) {
+    static __thread uint16_t cand[PORT_BLOCK];
+    int shift = 32 - __builtin_ctz(entries);
+    for (uint32_t w0 = 0; w0 < len; w0 += 32) {
+        uint32_t w1 = (w0 + 32 < len) ? w0 + 32 : len;
+        for (uint32_t p = w0; p < w1; p++)
+            cand[p] = (p + 4 <= len) ? table[hash32(rd32(in + p), shift)] : 0xffff;
+        for (uint32_t p = w0; p < w1; p++)
+            if (p + 4 <= len) table[hash32(rd32(in + p), shift)] = (uint16_t)p;
+    }
+    size_t op = 0;
+    uint32_t p = 1, next_emit = 0;
+    while (p + 4 <= len) {
+        uint32_t c = cand[p];
+        if (rd32(in + p - 1) == rd32(in + p)) c = p - 1;      /* a run beats the table candidate */
+        if (rd32(in + c) == rd32(in + p)) {
+            uint32_t m = 4 + common_prefix(in, c + 4, p + 4, len);
+            if (m > 1024) m = 1024;
+            if (p > next_emit) op = put_literal(out, op, in + next_emit, p - next_emit);
+            op = put_copy(out, op, p - c, m);
+            p += m;
+            next_emit = p;
+        } else {
+            p++;
+        }
+    }
+    if (next_emit < len) op = put_literal(out, op, in + next_emit, len - next_emit);
+    return op;
+}
+
+size_t port_fast_compress(const uint8_t *in, size_t n, uint8_t *out) {
+    static __thread uint16_t table[PORT_MAX_TABLE];
+    size_t op = port_varint32(out, (uint32_t)n);
+    size_t done = 0;
+    while (done < n) {
+        uint32_t len = (uint32_t)((n - done < PORT_BLOCK) ? (n - done) : PORT_BLOCK);
+        uint32_t entries = port_table_entries(len);
+        memset(table, 0, entries * sizeof(uint16_t));
+        op += port_fast_compress_fragment(in + done, len, out + op, table, entries);
+        done += len;
+    }
+    return op;
+}

@@ -71,6 +71,15 @@ class Port(_Lib):
                                              C.POINTER(C.c_size_t)]
         self.lib.port_table_entries.restype = C.c_uint32
         self.lib.port_table_entries.argtypes = [C.c_uint32]
+        self.lib.port_fast_compress.restype = C.c_size_t
+        self.lib.port_fast_compress.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p]
+
+    def fast_compress(self, data: bytes) -> bytes:
+        """Sequential model of libsnappy_b200's FAST mode (oracle/snappy_port.c, port_fast_compress):
+        defines that mode's stream; not a restatement of the reference."""
+        out = C.create_string_buffer(self.max_compressed_length(len(data)) + 16)
+        n = self.lib.port_fast_compress(data, len(data), out)
+        return out.raw[:n]
 
     def uncompress(self, data: bytes, cap: int) -> bytes:
         out = C.create_string_buffer(cap + 16)

@@ -41,8 +41,10 @@ def _worker(rank, world, port, n_total, q):
         sh = multi.ShardedStream(n_total, dev)
         shard = torch.from_numpy(host[sh.lo:sh.hi].copy()).to(dev)
         stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+        torch.cuda.synchronize()
         payload, size = ctx.compress_device(shard, header=False)
         dst = torch.zeros(pkg.max_compressed_length(n_total) + 16, dtype=torch.uint8, device=dev) if rank == 0 else None
+        torch.cuda.synchronize()      # the context's stream is non-blocking: order the allocations before it
         with torch.cuda.stream(stream):
             total = sh.assemble(payload, size, dst)
         torch.cuda.synchronize()
