@@ -120,6 +120,7 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.nseq = (uint32_t*)c->nseq.p;
     p.sizes = (uint32_t*)c->sizes.p;
     p.with_header = 0;
+    p.sparse = (mode == SNAPPY_B200_FAST);
     p.out = (uint8_t*)d_dst;
     p.out_stride = 0;
     p.offsets = (const unsigned long long*)c->offsets.p;
@@ -210,6 +211,7 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         p.nseq = (uint32_t*)c->nseq.p + f0;
         p.sizes = (uint32_t*)c->sizes.p + f0;
         p.with_header = 0;
+        p.sparse = (mode == SNAPPY_B200_FAST);
         p.out = d_out;
         p.out_stride = 0;
         p.offsets = (const unsigned long long*)c->offsets.p + f0;
@@ -399,6 +401,7 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.nseq = (uint32_t*)c->nseq.p;
     p.sizes = d_sizes;
     p.with_header = 1;
+    p.sparse = (mode == SNAPPY_B200_FAST);
     p.out = (uint8_t*)d_dst;
     p.out_stride = out_stride;
     p.offsets = nullptr;

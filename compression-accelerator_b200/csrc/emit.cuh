@@ -135,4 +135,146 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(JobParams p) {
     }
 }
 
+
+// ---- sparse (position-indexed) copy slots of the fast mode (parse_fast.cuh) ----------------------
+// Slot i of a job describes the copy that starts at position 4i + (slot & 3), if any:
+// offset << 16 | (len - 4) << 2 | (position & 3); zero = none.  The literal before a copy is the gap
+// since the end of the previous copy, so both kernels carry a running "end of the last copy"
+// (a prefix maximum: copy ends increase along the stream).
+__device__ __forceinline__ uint32_t sparse_pos(uint32_t slot_index, uint32_t v) { return (slot_index << 2) + (v & 3u); }
+__device__ __forceinline__ uint32_t sparse_len(uint32_t v) { return ((v >> 2) & 0x3fffu) + 4u; }
+__device__ __forceinline__ uint32_t sparse_off(uint32_t v) { return v >> 16; }
+__device__ __forceinline__ uint32_t sparse_slots(uint32_t len) { return (len + 3u) >> 2; }
+
+// encoded bytes of the literal [from, to) (nothing when empty)
+__device__ __forceinline__ uint32_t literal_encoded_size(uint32_t from, uint32_t to) {
+    return to > from ? literal_header_size(to - from) + (to - from) : 0u;
+}
+
+__global__ void __launch_bounds__(128) size_sparse_kernel(JobParams p) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (job >= p.n_jobs) return;
+    const uint32_t len = job_len_of(p, job);
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
+    const uint32_t n = sparse_slots(len);
+    uint32_t sum = 0, carry = 0;                             // carry = end of the last copy so far
+    for (uint32_t base = 0; base < n; base += 32) {
+        const uint32_t i = base + lane;
+        const uint32_t v = i < n ? q[i] : 0u;
+        const uint32_t pos = sparse_pos(i, v);
+        const uint32_t end = v ? pos + sparse_len(v) : 0u;
+        uint32_t x = end;                                    // inclusive prefix maximum of the ends
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(kFull, x, d);
+            if (lane >= d) x = max(x, y);
+        }
+        uint32_t before = __shfl_up_sync(kFull, x, 1);
+        before = lane ? max(before, carry) : carry;
+        if (v) sum += literal_encoded_size(before, pos) + copy_encoded_size(sparse_off(v), sparse_len(v));
+        carry = max(carry, __shfl_sync(kFull, x, 31));
+    }
+    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
+    sum += literal_encoded_size(carry, len);                 // trailing literal (snappy.cc:665-668)
+    if (lane == 0) p.sizes[job] = sum + (p.with_header ? varint32_len(len) : 0);
+}
+
+__global__ void __launch_bounds__(kEmitThreads) emit_sparse_kernel(JobParams p) {
+    __shared__ uint32_t warp_max[kEmitThreads / 32], warp_sum[kEmitThreads / 32];
+    __shared__ uint32_t carry_end_s, carry_out_s;
+    __shared__ uint32_t long_src[kMaxLong + 1], long_dst[kMaxLong + 1], long_len[kMaxLong + 1];
+    __shared__ uint32_t n_long;
+    const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t len = job_len_of(p, job);
+    const uint8_t* __restrict__ in = p.in + (uint64_t)job * p.in_stride;
+    uint8_t* __restrict__ out = p.out + (p.offsets ? p.offsets[job] : (uint64_t)job * p.out_stride);
+    const uint32_t* __restrict__ q = reinterpret_cast<const uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
+    const uint32_t n = sparse_slots(len);
+    uint32_t hdr = 0;
+    if (p.with_header) {
+        hdr = varint32_len(len);
+        if (tid == 0) put_varint32(out, len);
+    }
+    if (tid == 0) { carry_end_s = 0; carry_out_s = hdr; n_long = 0; }
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += kEmitThreads) {
+        const uint32_t i = base + tid;
+        const uint32_t v = i < n ? q[i] : 0u;
+        const uint32_t pos = sparse_pos(i, v), clen = sparse_len(v), off = sparse_off(v);
+        const uint32_t end = v ? pos + clen : 0u;
+        // block-wide exclusive prefix maximum of the copy ends -> start of my literal
+        uint32_t x = end;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(kFull, x, d);
+            if (lane >= d) x = max(x, y);
+        }
+        if (lane == 31) warp_max[wid] = x;
+        __syncthreads();
+        uint32_t before = __shfl_up_sync(kFull, x, 1);
+        if (lane == 0) before = 0;
+        before = max(before, carry_end_s);
+        for (uint32_t k = 0; k < wid; ++k) before = max(before, warp_max[k]);
+        const uint32_t lit = (v && pos > before) ? pos - before : 0u;
+        const uint32_t lh = lit ? literal_header_size(lit) : 0u;
+        const uint32_t osz = v ? lh + lit + copy_encoded_size(off, clen) : 0u;
+        // block-wide exclusive prefix sum of the encoded sizes -> my output position
+        uint32_t sx = osz;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(kFull, sx, d);
+            if (lane >= d) sx += y;
+        }
+        if (lane == 31) warp_sum[wid] = sx;
+        __syncthreads();
+        uint32_t op = carry_out_s + sx - osz;
+        for (uint32_t k = 0; k < wid; ++k) op += warp_sum[k];
+        const uint32_t tile_end_out = op + osz;              // meaningful in the last thread
+        if (lit) {                                           // snappy.cc:337-378 EmitLiteral
+            const uint32_t m = lit - 1;
+            if (m < 60) out[op] = (uint8_t)(m << 2);
+            else if (m < 256) { out[op] = 60u << 2; out[op + 1] = (uint8_t)m; }
+            else { out[op] = 61u << 2; out[op + 1] = (uint8_t)m; out[op + 2] = (uint8_t)(m >> 8); }
+            op += lh;
+            if (lit <= kShortLiteral) {
+                for (uint32_t b = 0; b < lit; ++b) out[op + b] = __ldg(in + before + b);
+            } else {
+                const uint32_t slot = atomicAdd(&n_long, 1u);
+                long_src[slot] = before; long_dst[slot] = op; long_len[slot] = lit;
+            }
+            op += lit;
+        }
+        if (v) {                                             // snappy.cc:402-431 EmitCopy
+            uint32_t rem = clen;
+            if (rem >= 12) {
+                while (rem >= 68) { op += put_copy_le64(out + op, off, 64, false); rem -= 64; }
+                if (rem > 64) { op += put_copy_le64(out + op, off, 60, false); rem -= 60; }
+            }
+            put_copy_le64(out + op, off, rem, rem < 12);
+        }
+        __syncthreads();
+        const uint32_t nl = n_long;
+        for (uint32_t k = 0; k < nl; ++k)
+            block_copy(out + long_dst[k], in + long_src[k], long_len[k], tid, kEmitThreads);
+        __syncthreads();
+        if (tid == kEmitThreads - 1) {
+            carry_end_s = max(max(before, end), carry_end_s);
+            carry_out_s = tile_end_out;
+            n_long = 0;
+        }
+        __syncthreads();
+    }
+    // trailing literal (snappy.cc:665-668)
+    const uint32_t from = carry_end_s;
+    if (from < len) {
+        const uint32_t lit = len - from, m = lit - 1;
+        uint32_t op = carry_out_s;
+        if (tid == 0) {
+            if (m < 60) out[op] = (uint8_t)(m << 2);
+            else if (m < 256) { out[op] = 60u << 2; out[op + 1] = (uint8_t)m; }
+            else { out[op] = 61u << 2; out[op + 1] = (uint8_t)m; out[op + 2] = (uint8_t)(m >> 8); }
+        }
+        op += literal_header_size(lit);
+        block_copy(out + op, in + from, lit, tid, kEmitThreads);
+    }
+}
+
 }  // namespace sb

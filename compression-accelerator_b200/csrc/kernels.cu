@@ -186,38 +186,27 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
 __global__ void __launch_bounds__(32 * (2 + kFastMaxK), 2) parse_fast_kernel(JobParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NT = blockDim.x;
-    // Roles.  Small CTAs (batch path): warp 0 = table, 1 = chaser, 2.. = evaluators.  The 16-warp
-    // CTA of the stream path keeps one scheduler (warps 0,4,8,12 share an SM sub-partition) for the
-    // two sequential roles -- table = warp 0, chaser = warp 4, warps 8 and 12 retire at once -- and
-    // puts the 12 evaluators on the other three, so that waiting evaluators cannot take issue
-    // slots from the roles every other warp waits for.
-#ifndef SB_FAST_SPREAD
-#define SB_FAST_SPREAD 1
-#endif
-    const bool spread = SB_FAST_SPREAD && NT == 512;
-#ifndef SB_FAST_KUSE
-#define SB_FAST_KUSE 12u
-#endif
-    const uint32_t K = spread ? SB_FAST_KUSE : (NT >> 5) - 2;
-    const uint32_t role_t = 0, role_c = spread ? 4u : 1u;
-    const uint32_t e_idx = spread ? wid - 1 - (wid >> 2) : wid - 2;
-    const bool idle = spread && (wid == 8 || wid == 12 || ((wid & 3u) && e_idx >= K));
+    // Roles: warp 0 = table, warp 1 = chaser, warps 2.. = evaluators.
+    const uint32_t K = (NT >> 5) - 2;
+    const uint32_t role_t = 0, role_c = 1;
+    const uint32_t e_idx = wid - 2;
+    const bool idle = false;
     const uint32_t job = blockIdx.x;
-    const FastLayout lay = fast_layout(p.job_len, K);
+    const FastLayout lay = fast_layout(p.job_len);
     FastCtl* ctl = reinterpret_cast<FastCtl*>(smem);
     uint16_t* table = reinterpret_cast<uint16_t*>(smem + lay.table);
     uint16_t* cring = reinterpret_cast<uint16_t*>(smem + lay.cring);
     uint32_t* ering = reinterpret_cast<uint32_t*>(smem + lay.ering);
-    unsigned long long* ans = reinterpret_cast<unsigned long long*>(smem + lay.ans);
+    uint8_t* entry = smem + lay.entry;
     uint8_t* s_in = smem + lay.input;
     const uint32_t len = job_len_of(p, job);
     const uint32_t entries = table_entries(len);
+    const uint32_t nwin = (len + 31) >> 5;
     const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
 
     const uint32_t bulk = (((uintptr_t)src & 15u) == 0) ? (len & ~15u) : 0u;
     if (tid == 0) {
-        ctl->t_done = 0; ctl->c_win = 0;
-        for (int i = 0; i < 16; ++i) ctl->done[i] = 0;
+        ctl->t_done = 0;
         if (bulk) {                                          // TMA bulk copy of the 16-byte aligned body
             mbar_init(&ctl->bar, 1);
             mbar_expect_tx(&ctl->bar, bulk);
@@ -228,49 +217,45 @@ __global__ void __launch_bounds__(32 * (2 + kFastMaxK), 2) parse_fast_kernel(Job
         uint4* t4 = reinterpret_cast<uint4*>(table);
         const uint4 z = make_uint4(0, 0, 0, 0);
         for (uint32_t i = tid; i < entries / 8; i += NT) t4[i] = z;
-        for (uint32_t i = tid; i < 2 * K * 32; i += NT) ering[i] = 0;
-        for (uint32_t i = tid; i < kAnsRing; i += NT) ans[i] = 0ull;
+        for (uint32_t i = tid; i < kRecRing * 32; i += NT) ering[i] = 0;
+        for (uint32_t i = tid; i < nwin; i += NT) entry[i] = (uint8_t)kEntryNone;
         for (uint32_t i = bulk + tid; i < len; i += NT) s_in[i] = src[i];
         const uint32_t padded = ((len + 15u) & ~15u) + kFastPad;
         for (uint32_t i = len + tid; i < padded; i += NT) s_in[i] = 0;
     }
     __syncthreads();
     if (bulk) mbar_wait(&ctl->bar, 0);
+    if (idle) return;
 
     const int shift = 32 - (31 - __clz(entries));
-    const uint32_t nwin = (len + 31) >> 5;
-    seq_t* seqs = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+    uint32_t* slots = reinterpret_cast<uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
 #ifdef SNAPPY_B200_STATS
     const long long t_start = clock64();
 #endif
     FSTAT_DECL();
-    if (idle) return;
     if (wid == role_t) {
-        fast_table_warp(s_in, len, nwin, table, shift, cring, ctl, (int)lane FSTAT_ARG);
+        fast_table_warp(s_in, len, nwin, table, shift, cring, entry, ctl, (int)lane FSTAT_ARG);
         FSTAT_FLUSH(1, 1, lane);
 #ifdef SNAPPY_B200_STATS
         if (lane == 0) { atomicAdd(&g_stats[0], (unsigned long long)(clock64() - t_start)); atomicAdd(&g_stats[9], 1ull); }
 #endif
     } else if (wid == role_c) {
-        const uint32_t n = fast_chaser(ering, ans, ctl, nwin, K, len, seqs, (int)lane FSTAT_ARG);
-        if (lane == 0) p.nseq[job] = n;
-        FSTAT_FLUSH(2, 6, lane); FSTAT_FLUSH(3, 8, lane); FSTAT_FLUSH(0, 10, lane); FSTAT_FLUSH(1, 11, lane);
+        fast_chaser(ering, entry, nwin, 2 * K, (int)lane FSTAT_ARG);
+        FSTAT_FLUSH(2, 6, lane); FSTAT_FLUSH(3, 8, lane);
 #ifdef SNAPPY_B200_STATS
         if (lane == 0) atomicAdd(&g_stats[7], (unsigned long long)(clock64() - t_start));
 #endif
     } else {
-        const uint32_t e = e_idx;
         FastWin prev;
         prev.live = false;
-        for (uint32_t i = 0, w = e;; ++i, w += K) {
+        for (uint32_t i = 0, w = e_idx;; ++i, w += K) {
             FastWin cur;
             cur.live = false;
-            if (w < nwin) fast_evaluate(s_in, len, cring, ering, ctl, w, e + K * (i & 1u), cur, (int)lane FSTAT_ARG);
-            if (prev.live) fast_emit(ans, &ctl->done[e], seqs, prev, (int)lane FSTAT_ARG);
+            if (w < nwin) fast_evaluate(s_in, len, cring, ering, entry, ctl, w, e_idx + K * (i & 1u), cur, (int)lane FSTAT_ARG);
+            if (prev.live) fast_emit(entry, slots, prev, (int)lane FSTAT_ARG);
             if (!cur.live) break;
             prev = cur;
         }
-        if (lane == 0) ctl->done[e] = 0xffffffffu;               // nothing left to emit
         FSTAT_FLUSH(2, 2, lane); FSTAT_FLUSH(3, 3, lane); FSTAT_FLUSH(0, 4, lane); FSTAT_FLUSH(1, 5, lane);
     }
 }
@@ -376,7 +361,7 @@ cudaError_t kernels_init() {
                              (int)pipe_smem_bytes<true>(kBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(parse_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)fast_layout(kBlock, kFastMaxK).total);
+                                (int)fast_layout(kBlock).total);
 }
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
@@ -384,7 +369,7 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
     if (p.n_jobs == 0) return cudaSuccess;
     if (mode == 1) {
         const uint32_t K = fast_evaluators(p.job_len);      // 14 -> the 16-warp CTA (12 of them evaluate)
-        parse_fast_kernel<<<p.n_jobs, 32 * (2 + K), fast_layout(p.job_len, K).total, st>>>(p);
+        parse_fast_kernel<<<p.n_jobs, 32 * (2 + K), fast_layout(p.job_len).total, st>>>(p);
     } else if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     else if (mode == 0 && p.job_len > 16384)   // small jobs fit many per SM: the single-warp parser wins
         parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
@@ -397,14 +382,16 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
 
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
-    size_kernel<<<(p.n_jobs + 3) / 4, 128, 0, st>>>(p);
+    if (p.sparse) size_sparse_kernel<<<(p.n_jobs + 3) / 4, 128, 0, st>>>(p);
+    else size_kernel<<<(p.n_jobs + 3) / 4, 128, 0, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }
 
 cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
-    emit_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
+    if (p.sparse) emit_sparse_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
+    else emit_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -38,6 +38,7 @@ struct JobParams {
     uint32_t* nseq;        // number of sequences of job j
     uint32_t* sizes;       // encoded bytes of job j (header included when with_header)
     uint32_t with_header;  // 1: each job is its own stream and starts with varint32(len)
+    uint32_t sparse;       // 1: seqs holds the fast mode's position-indexed copy slots (parse_fast.cuh)
     // emit destination: job j writes at out + (offsets ? offsets[j] : j*out_stride)
     uint8_t* out;
     uint64_t out_stride;

@@ -2,7 +2,7 @@
 //
 // The exact parse (parse_pipe.cuh) is sequential because Snappy inserts a position into its hash
 // table only if the parse probes it (tests/snappy/snappy.cc:587-659).  The fast mode drops that
-// one rule -- EVERY position is looked up and inserted, in position order -- and with it the
+// one rule -- EVERY position is looked up and inserted, window by window -- and with it the
 // dependence of the table on the parse.  What is left splits into three roles that run as a
 // pipeline over the fragment's 32-position windows, the fragment staged in shared memory by TMA:
 //
@@ -13,12 +13,17 @@
 //   evaluator warps (K) take windows round-robin: 4-byte compare and match extension against
 //                       cand(p) (snappy-internal.h:95-143; 16-byte compares per lane up to 64 bytes,
 //                       warp-cooperative beyond), then -- by pointer jumping over the lanes -- for
-//                       every possible entry lane of the window the end of the last copy and the
-//                       number of copies the greedy parse takes from there.
-//   chaser warp (1)     the only sequential step: one shared-memory look-up per window maps the
-//                       entry lane to the next window's entry lane; it hands every window its
-//                       entry, sequence index and literal start, and the window's evaluator
-//                       writes the sequences (one shuffle per copy).
+//                       every possible entry lane of the window where the greedy parse leaves it.
+//   chaser warp (1)     the only sequential step, kept to a dozen instructions per window (a lone
+//                       warp issues one dependent instruction every ~10 cycles): one shuffle maps
+//                       the entry lane to the next window's entry lane; it records every window's
+//                       entry lane, and the window's evaluator then writes the window's copies.
+//
+// Copies go to a position-indexed ("sparse") list: a copy starting at position p owns slot p / 4
+// (copies are >= 4 bytes long, so slots never collide and stay in stream order); every window's
+// evaluator writes the window's 8 slots, empty ones as zero.  Literal lengths are the gaps between
+// consecutive copies and are recovered by the size / emit kernels (emit.cuh), so the sequential
+// step carries neither a sequence count nor a literal start.
 //
 // The stream is a valid Snappy stream, deterministic, and defined by the sequential model
 // port_fast_compress (oracle/snappy_port.c), against which tests pin it byte for byte; its size
@@ -35,26 +40,28 @@ namespace sb {
 constexpr uint32_t kFastCap = 1024;        // longest match reported (model: min(prefix, 1024))
 constexpr uint32_t kFastLane = 64;         // per-lane extension limit; longer matches go cooperative
 constexpr uint32_t kCandRing = 64;         // windows the table warp may run ahead of the chaser
-constexpr uint32_t kFastMaxK = 14;         // evaluator warps per CTA (stream path)
+constexpr uint32_t kRecRing = 64;          // record slots allocated; 2K are used: evaluator e owns slots e and e + K,
+                                           // so a late record of a window the chaser jumped over can never land on
+                                           // another warp's record
+#ifndef SB_FAST_K
+#define SB_FAST_K 14
+#endif
+constexpr uint32_t kFastMaxK = SB_FAST_K;  // evaluator warps of the stream path (+ table warp + chaser warp)
 constexpr uint32_t kNoCand = 0xffffu;
-// Answers of the chaser live in a ring of 64.  Chains of long copies let the chaser run arbitrarily
-// far ahead of a slow evaluator (it needs only one evaluated window per copy), so every evaluator
-// publishes how far it has emitted (FastCtl::done) and the chaser never writes the answer of window
-// v before every window <= v - 64 has been emitted; it re-reads the progress words only when it
-// reaches that bound.
-constexpr uint32_t kAnsRing = 64;
 constexpr uint32_t kFastPad = 96;          // zeroed slack after the input: 16-byte reads up to pos+80
+constexpr uint32_t kEntryNone = 0xffu;     // entry[] : chaser has not reached the window
+constexpr uint32_t kEntrySkip = 0xfeu;     // entry[] : window lies wholly inside a copy
 
 struct FastLayout {                        // byte offsets into dynamic shared memory
-    uint32_t table, cring, ering, ans, input, total;
+    uint32_t table, cring, ering, entry, input, total;
 };
-__host__ __device__ inline FastLayout fast_layout(uint32_t job_len, uint32_t K) {
+__host__ __device__ inline FastLayout fast_layout(uint32_t job_len) {
     FastLayout l;
     l.table = 128;
     l.cring = l.table + table_entries(job_len) * 2;
     l.ering = l.cring + kCandRing * 32 * 2;
-    l.ans = l.ering + 2 * K * 32 * 4;
-    l.input = (l.ans + kAnsRing * 8 + 15u) & ~15u;
+    l.entry = l.ering + kRecRing * 32 * 4;
+    l.input = (l.entry + ((job_len + 31u) >> 5) + 15u) & ~15u;
     l.total = l.input + ((job_len + 15u) & ~15u) + kFastPad;
     return l;
 }
@@ -65,9 +72,42 @@ __host__ __device__ inline uint32_t fast_evaluators(uint32_t job_len) {
 struct FastCtl {                           // first 128 bytes of shared memory
     uint64_t bar;                          // mbarrier of the TMA load
     volatile uint32_t t_done;              // windows whose candidates are in the ring
-    volatile uint32_t c_win;               // chaser progress (flow control only, may lag)
-    volatile uint32_t done[16];            // per evaluator: all its windows below this index are emitted
 };
+
+// sparse sequence slot: offset << 16 | (len - 4) << 2 | (position & 3); 0 = no copy starts here
+__host__ __device__ inline uint32_t sparse_pack(uint32_t pos, uint32_t len, uint32_t off) {
+    return (off << 16) | ((len - 4) << 2) | (pos & 3u);
+}
+
+#ifdef SNAPPY_B200_STATS
+// cycle accumulators live in registers (fs_acc[]) and reach g_stats once per role and fragment
+#define FSTAT_T0() const long long fs_t0 = clock64()
+#define FSTAT_ADD(i, lane) do { fs_acc[(i) & 3] += (unsigned long long)(clock64() - fs_t0); } while (0)
+#define FSTAT_DECL() unsigned long long fs_acc[4] = {0, 0, 0, 0}
+#define FSTAT_PARAM , unsigned long long* fs_acc
+#define FSTAT_ARG , fs_acc
+#define FSTAT_FLUSH(slot, i, lane) do { if ((lane) == 0) atomicAdd(&g_stats[i], fs_acc[(slot) & 3]); } while (0)
+#else
+#define FSTAT_DECL() do {} while (0)
+#define FSTAT_PARAM
+#define FSTAT_ARG
+#define FSTAT_FLUSH(slot, i, lane) do {} while (0)
+#define FSTAT_T0() do {} while (0)
+#define FSTAT_ADD(i, lane) do {} while (0)
+#endif
+#ifndef SB_FAST_TGROUP
+#define SB_FAST_TGROUP 8
+#endif
+#ifndef SB_FAST_SLEEP
+#define SB_FAST_SLEEP 32
+#endif
+__device__ __forceinline__ void fast_backoff() {
+#if SB_FAST_SLEEP > 0
+    __nanosleep(SB_FAST_SLEEP);          // waiting warps must not eat the issue slots of the sequential roles
+#endif
+}
+#define FAST_WATCHDOG(spins, what, a, b)                                                          \
+    do { if ((spins) > (1u << 24)) { if (lane == 0) printf("fast: %s blk %d %u %u\n", what, blockIdx.x, (unsigned)(a), (unsigned)(b)); __trap(); } } while (0)
 
 // common prefix of s[a..] and s[b..] (b < end), at most `cap`, 128 bytes per round
 __device__ __forceinline__ uint32_t coop_match_capped(const uint8_t* s, uint32_t a, uint32_t b,
@@ -102,62 +142,45 @@ __device__ __forceinline__ uint32_t prefix16(uint32_t x0, uint32_t x1, uint32_t 
 }
 
 // ---- table warp ---------------------------------------------------------------------------------
-#ifdef SNAPPY_B200_STATS
-// cycle accumulators live in registers (fs_acc[]) and reach g_stats once per role and fragment
-#define FSTAT_T0() const long long fs_t0 = clock64()
-#define FSTAT_ADD(i, lane) do { fs_acc[(i) & 3] += (unsigned long long)(clock64() - fs_t0); } while (0)
-#define FSTAT_DECL() unsigned long long fs_acc[4] = {0, 0, 0, 0}
-#define FSTAT_PARAM , unsigned long long* fs_acc
-#define FSTAT_ARG , fs_acc
-#define FSTAT_FLUSH(slot, i, lane) do { if ((lane) == 0) atomicAdd(&g_stats[i], fs_acc[(slot) & 3]); } while (0)
-#else
-#define FSTAT_DECL() do {} while (0)
-#define FSTAT_PARAM
-#define FSTAT_ARG
-#define FSTAT_FLUSH(slot, i, lane) do {} while (0)
-#define FSTAT_T0() do {} while (0)
-#define FSTAT_ADD(i, lane) do {} while (0)
-#endif
-#ifndef SB_FAST_TGROUP
-#define SB_FAST_TGROUP 8
-#endif
-#ifndef SB_FAST_SLEEP
-#define SB_FAST_SLEEP 32
-#endif
-__device__ __forceinline__ void fast_backoff() {
-#if SB_FAST_SLEEP > 0
-    __nanosleep(SB_FAST_SLEEP);          // waiting warps must not eat the issue slots of the sequential roles
-#endif
+// One window of the table walk.  Lanes run DOWN the window: when several lanes of one store
+// instruction hit the same shared-memory address, B200 keeps the LOWEST lane's value (measured:
+// scripts/probes/sts_conflict.cu; CUDA leaves it unspecified), so with this mapping the highest
+// position of a slot stays, as in the model.  Any other arbitration would still give a valid stream,
+// only not the model's bytes -- the parity tests would say so.
+__device__ __forceinline__ void fast_table_window(const uint8_t* s, uint32_t len, uint32_t w,
+                                                  uint16_t* table, int shift, uint16_t* cring, uint32_t rl) {
+    const uint32_t pos = (w << 5) + rl;
+    const bool valid = pos + 4 <= len;
+    const uint32_t h = hash32(lds32u(s, pos), shift);
+    uint32_t T = kNoCand;
+    if (valid) {
+        T = table[h];                         // state after the previous window: always < this window
+        table[h] = (uint16_t)pos;
+    }
+    cring[((w & (kCandRing - 1)) << 5) + rl] = (uint16_t)(pos ? T : kNoCand);
 }
 
 __device__ __forceinline__ void fast_table_warp(const uint8_t* s, uint32_t len, uint32_t nwin,
                                                 uint16_t* table, int shift, uint16_t* cring,
-                                                FastCtl* ctl, int lane FSTAT_PARAM) {
+                                                const volatile uint8_t* entry, FastCtl* ctl,
+                                                int lane FSTAT_PARAM) {
+    const uint32_t rl = 31u - lane;
     for (uint32_t w0 = 0; w0 < nwin; w0 += SB_FAST_TGROUP) {
         const uint32_t w1 = min(w0 + SB_FAST_TGROUP, nwin);
-        if (w1 > kCandRing) {
+        if (w1 > kCandRing) {                 // the slot of window w1-1 still belongs to window w1-1-64
             FSTAT_T0();
-            for (uint32_t spins = 0; w1 > ctl->c_win + kCandRing; ++spins) {
+            for (uint32_t spins = 0; entry[w1 - 1 - kCandRing] == kEntryNone; ++spins) {
                 fast_backoff();
-                if (spins > (1u << 24)) { if (lane == 0) printf("fast: table warp stuck blk %d w1 %u c_win %u t_done %u\n", blockIdx.x, w1, ctl->c_win, ctl->t_done); __trap(); }
+                FAST_WATCHDOG(spins, "table warp waits for the chaser", w1, ctl->t_done);
             }
             FSTAT_ADD(1, lane);
         }
-        for (uint32_t w = w0; w < w1; ++w) {
-            // Lanes run DOWN the window.  When several lanes of one store instruction hit the same
-            // shared-memory address, B200 keeps the LOWEST lane's value (measured:
-            // scripts/probes/sts_conflict.cu; CUDA leaves it unspecified), so with this mapping the
-            // highest position of a slot stays, as in the model.  Any other arbitration would still
-            // give a valid stream, only not the model's bytes -- the parity tests would say so.
-            const uint32_t rl = 31u - lane, pos = (w << 5) + rl;
-            const bool valid = pos + 4 <= len;
-            const uint32_t h = hash32(lds32u(s, pos), shift);
-            uint32_t T = kNoCand;
-            if (valid) {
-                T = table[h];                 // state after the previous window: always < this window
-                table[h] = (uint16_t)pos;
-            }
-            cring[((w & (kCandRing - 1)) << 5) + rl] = (uint16_t)(pos ? T : kNoCand);
+        if (w1 - w0 == SB_FAST_TGROUP) {      // a lone warp lives on instruction-level parallelism:
+#pragma unroll                                // the windows' loads and hashes overlap, only the
+            for (uint32_t k = 0; k < SB_FAST_TGROUP; ++k)   // table accesses keep their order
+                fast_table_window(s, len, w0 + k, table, shift, cring, rl);
+        } else {
+            for (uint32_t w = w0; w < w1; ++w) fast_table_window(s, len, w, table, shift, cring, rl);
         }
         __threadfence_block();
         __syncwarp();
@@ -167,17 +190,17 @@ __device__ __forceinline__ void fast_table_warp(const uint8_t* s, uint32_t len, 
 
 // ---- evaluator ------------------------------------------------------------------------------------
 struct FastWin {                           // what an evaluator keeps of a window until it emits it
-    uint32_t w, slot, L, imm, mo;          // imm = next taken lane | end lane << 6 ; mo = len | offset << 16
+    uint32_t w, L, imm, mo;                // imm = next taken lane | end lane << 6 ; mo = len | offset << 16
     bool live;
 };
 
 __device__ __forceinline__ void fast_evaluate(const uint8_t* s, uint32_t len, const uint16_t* cring,
-                                              uint32_t* ering, FastCtl* ctl, uint32_t w, uint32_t slot,
-                                              FastWin& st, int lane FSTAT_PARAM) {
+                                              uint32_t* ering, const volatile uint8_t* entry,
+                                              FastCtl* ctl, uint32_t w, uint32_t slot, FastWin& st,
+                                              int lane FSTAT_PARAM) {
+    // (the record slot is free: this warp has already emitted the window that used it, w - 2K)
     FSTAT_T0();
-    for (uint32_t spins = 0; ctl->t_done <= w; ++spins) {
-        if (spins > (1u << 24)) { if (lane == 0) printf("fast: evaluator stuck on t_done blk %d w %u c_win %u t_done %u\n", blockIdx.x, w, ctl->c_win, ctl->t_done); __trap(); }
-    }
+    for (uint32_t spins = 0; ctl->t_done <= w; ++spins) FAST_WATCHDOG(spins, "evaluator waits for candidates", w, ctl->t_done);
     __syncwarp();
     FSTAT_ADD(2, lane);
     const uint32_t pos = (w << 5) + lane;
@@ -228,138 +251,122 @@ __device__ __forceinline__ void fast_evaluate(const uint8_t* s, uint32_t len, co
         const uint32_t mm = L & (kFull << ek);
         if (mm) nxt = __ffs(mm) - 1;
     }
-    st.w = w; st.slot = slot; st.L = L; st.live = true;
+    st.w = w; st.L = L; st.live = true;
     st.imm = nxt | (ek << 6);
     st.mo = m | (off << 16);
-    // pointer jumping: pk = next lane (32 = end of chain) | end of the chain's last copy << 6 | copies << 17
-    uint32_t pk = nxt | (ek << 6) | (1u << 17);
+    // pointer jumping (a chain has at most 8 copies): pk = next lane (32 = end of chain) | end lane of
+    // the chain's last copy << 6
+    uint32_t pk = nxt | (ek << 6);
 #pragma unroll
     for (int round = 0; round < 3; ++round) {
         const uint32_t q = __shfl_sync(kFull, pk, pk & 31u);
-        if ((pk & 63u) < 32u) pk = (q & 0x1ffffu) + ((pk >> 17) + (q >> 17) << 17);
+        if ((pk & 63u) < 32u) pk = q;
     }
+    // record of entry lane `lane`: where the parse enters the following windows
     const uint32_t me = L & (kFull << lane);
     const uint32_t q = __shfl_sync(kFull, pk, me ? __ffs(me) - 1 : 0);
-    const uint32_t rec = me ? ((q >> 6) & 0x7ffu) | ((q >> 17) << 11) : 0u;
+    const uint32_t E = me ? (q >> 6) : 0u;                          // end of the last copy taken (0: none)
+    const uint32_t rec = E >= 32 ? (E & 31u) | (((E - 32) >> 5) << 5) : 0u;   // next entry lane | windows skipped << 5
     reinterpret_cast<volatile uint32_t*>(ering)[(slot << 5) + lane] = ((w + 1) << 16) | rec;
     FSTAT_ADD(3, lane);      // wait + compute
 }
 
-// answers of the chaser: tag (window + 1) : 12 | skipped : 1 | entry lane : 5 | sequence index : 15 | literal start : 17
-__device__ __forceinline__ unsigned long long fast_ans_pack(uint32_t w, uint32_t skipped, uint32_t e,
-                                                            uint32_t sb, uint32_t ne) {
-    return (unsigned long long)((w + 1) & 0xfffu) | ((unsigned long long)skipped << 12) |
-           ((unsigned long long)e << 13) | ((unsigned long long)sb << 18) | ((unsigned long long)ne << 33);
-}
-
-__device__ __forceinline__ void fast_emit(const volatile unsigned long long* ans, volatile uint32_t* done,
-                                          seq_t* seqs, const FastWin& st, int lane FSTAT_PARAM) {
-    unsigned long long a;
+// The window's 8 sparse slots: the copies the parse takes when it enters the window at lane e.
+__device__ __forceinline__ void fast_emit(const volatile uint8_t* entry, uint32_t* slots,
+                                          const FastWin& st, int lane FSTAT_PARAM) {
+    uint32_t e;
     FSTAT_T0();
     for (uint32_t spins = 0;; ++spins) {
-        a = ans[st.w & (kAnsRing - 1)];
-        if ((uint32_t)(a & 0xfffu) == ((st.w + 1) & 0xfffu)) break;
+        e = entry[st.w];
+        if (e != kEntryNone) break;
         fast_backoff();
-        if (spins > (1u << 24)) { if (lane == 0) printf("fast: evaluator stuck on answer blk %d w %u ans %llx\n", blockIdx.x, st.w, a); __trap(); }
+        FAST_WATCHDOG(spins, "evaluator waits for its entry lane", st.w, 0);
     }
     __syncwarp();
-    FSTAT_ADD(4, lane);
-    if (lane == 0) *done = st.w + 1;                              // the answer is read: its slot may be reused
-    if ((a >> 12) & 1u) return;                                   // window lies inside a copy
-    const uint32_t e = (uint32_t)(a >> 13) & 31u;
-    uint32_t idx = (uint32_t)(a >> 18) & 0x7fffu, cur = (uint32_t)(a >> 33) & 0x1ffffu;
-    const uint32_t wbase = st.w << 5, pos = wbase + lane;
-    const uint32_t me = st.L & (kFull << e);
-    uint32_t f = me ? __ffs(me) - 1 : 32;
-    while (f < 32) {                                              // one shuffle per copy
-        if ((uint32_t)lane == f) seqs[idx] = seq_pack(pos - cur, st.mo & 0xffffu, st.mo >> 16);
-        const uint32_t t = __shfl_sync(kFull, st.imm, f);
-        cur = wbase + (t >> 6);
-        f = t & 63u;
-        ++idx;
+    FSTAT_ADD(0, lane);
+    uint32_t chosen = 0;
+    if (e != kEntrySkip) {
+        const uint32_t me = st.L & (kFull << e);
+        uint32_t f = me ? __ffs(me) - 1 : 32;
+        while (f < 32) {                                          // one shuffle per copy
+            chosen |= 1u << f;
+            f = __shfl_sync(kFull, st.imm, f) & 63u;
+        }
     }
-    FSTAT_ADD(5, lane);
+    // slot j (lane j < 8) holds the copy that starts in lanes 4j .. 4j+3, if any
+    const uint32_t mine = sparse_pack(lane, st.mo & 0xffffu, st.mo >> 16);
+    const uint32_t grp = (chosen >> ((lane & 7u) << 2)) & 15u;
+    const uint32_t v = __shfl_sync(kFull, mine, ((lane & 7u) << 2) + (grp ? __ffs(grp) - 1 : 0));
+    if (lane < 8) slots[(st.w << 3) + lane] = grp ? v : 0u;
+    FSTAT_ADD(1, lane);
 }
 
 // ---- chaser ---------------------------------------------------------------------------------------
-// Windows whose answers may be written: v < (lowest emitted-progress word) + kAnsRing.
-__device__ __forceinline__ uint32_t fast_safe_bound(FastCtl* ctl, uint32_t K, uint32_t w, int lane) {
-    for (uint32_t spins = 0;; ++spins) {
-        const uint32_t d = (uint32_t)lane < K ? ctl->done[lane] : 0xffffffffu;
-        const uint32_t m = __reduce_min_sync(kFull, d);
-        if (m > 0xffffffffu - kAnsRing) return 0xffffffffu;
-        if (w < m + kAnsRing) return m + kAnsRing;
-        if (spins > (1u << 26)) { if (lane == 0) printf("fast: chaser waits for emitters blk %d w %u min %u\n", blockIdx.x, w, m); __trap(); }
+// One window at a time; returns when `stop` is reached (or the fragment ends).
+__device__ __forceinline__ void fast_chase_steps(const volatile uint32_t* er, volatile uint8_t* entry,
+                                                 uint32_t nwin, uint32_t R, uint32_t stop, uint32_t& w,
+                                                 uint32_t& e, uint32_t& slot, int lane FSTAT_PARAM) {
+    while (w < nwin && w < stop) {
+        uint32_t v;
+        for (uint32_t spins = 0;; ++spins) {
+            v = __shfl_sync(kFull, er[(slot << 5) + lane], e);
+            if ((v >> 16) == w + 1) break;                         // else: record not published yet
+            FAST_WATCHDOG(spins, "chaser waits for a record", w, e);
+        }
+        entry[w] = (uint8_t)e;                                     // all lanes store the same byte
+        ++w;
+        slot = slot + 1 == R ? 0 : slot + 1;
+        e = v & 31u;
+        const uint32_t adv = (v >> 5) & 63u;
+        if (adv) {                                                 // windows wholly inside the copy
+            const uint32_t w2 = min(w + adv, nwin);
+            for (uint32_t x = w + lane; x < w2; x += 32) entry[x] = (uint8_t)kEntrySkip;
+            slot = (slot + (w2 - w)) % R;
+            w = w2;
+        }
     }
 }
 
-__device__ __forceinline__ uint32_t fast_chaser(const uint32_t* ering, volatile unsigned long long* ans,
-                                                FastCtl* ctl, uint32_t nwin, uint32_t K, uint32_t len,
-                                                seq_t* seqs, int lane FSTAT_PARAM) {
+// The sequential step, four windows per round: the rows of the next four windows are read at once,
+// the entry lane is pushed through them with four dependent shuffles, and only then are the four
+// records validated together (all published, no copy jumping over a whole window).  A round that
+// does not validate is redone window by window.  Nothing but the shuffles sits on the chain.
+__device__ __forceinline__ void fast_chaser(const uint32_t* ering, volatile uint8_t* entry,
+                                            uint32_t nwin, uint32_t R, int lane FSTAT_PARAM) {
     const volatile uint32_t* er = reinterpret_cast<const volatile uint32_t*>(ering);
-    const uint32_t R = 2 * K;
-    uint32_t w = 0, e = 0, ne = 0, sb = 0, slot = 0, safe = kAnsRing;
-    uint32_t row = nwin ? er[lane] : 0u;                           // lane l holds the record of entry lane l
-    while (w < nwin) {
-#ifdef SNAPPY_B200_STATS
-        const long long tc0 = clock64();
-#endif
-        uint32_t v = __shfl_sync(kFull, row, e);
-#ifdef SNAPPY_B200_STATS
-        const long long tc1 = clock64(); fs_acc[0] += (unsigned long long)(tc1 - tc0);
-#endif
-        if ((v >> 16) != w + 1) {                                  // record not published yet
-            FSTAT_T0();
-            for (uint32_t spins = 0;; ++spins) {
-                row = er[(slot << 5) + lane];
-                v = __shfl_sync(kFull, row, e);
-                if ((v >> 16) == w + 1) break;
-                if (spins > (1u << 26)) { if (lane == 0) printf("fast: chaser stuck blk %d w %u e %u v %x t_done %u\n", blockIdx.x, w, e, v, ctl->t_done); __trap(); }
-            }
-            FSTAT_ADD(6, lane);
-        }
+    uint32_t w = 0, e = 0, slot = 0;                               // slot = w mod R
+    while (w + 4 <= nwin) {
+        const uint32_t s1 = slot + 1 >= R ? slot + 1 - R : slot + 1;
+        const uint32_t s2 = slot + 2 >= R ? slot + 2 - R : slot + 2;
+        const uint32_t s3 = slot + 3 >= R ? slot + 3 - R : slot + 3;
+        const uint32_t r0 = er[(slot << 5) + lane], r1 = er[(s1 << 5) + lane];
+        const uint32_t r2 = er[(s2 << 5) + lane], r3 = er[(s3 << 5) + lane];
+        const uint32_t v0 = __shfl_sync(kFull, r0, e);
+        const uint32_t v1 = __shfl_sync(kFull, r1, v0);            // shuffles use the index modulo 32
+        const uint32_t v2 = __shfl_sync(kFull, r2, v1);
+        const uint32_t v3 = __shfl_sync(kFull, r3, v2);
+        // tags are w+1 .. w+4 in bits 16.., skips in bits 5..10: one compare per record
+        const uint32_t t = (w + 1) << 16;
+        const bool ok = ((v0 ^ t) < 32u) & ((v1 ^ (t + 0x10000u)) < 32u) & ((v2 ^ (t + 0x20000u)) < 32u) &
+                        ((v3 ^ (t + 0x30000u)) < 32u);
 #ifdef SNAPPY_B200_STATS
         fs_acc[3] += 1;
 #endif
-        const uint32_t nslot = slot + 1 == R ? 0 : slot + 1;
-        const uint32_t row_next = er[(nslot << 5) + lane];         // prefetch: usually ready long before
-        const uint32_t E = v & 0x7ffu, cnt = (v >> 11) & 15u;      // end of the last copy, copies taken
-        if (w >= safe) safe = fast_safe_bound(ctl, K, w, lane);
-#ifdef SNAPPY_B200_STATS
-        const long long tc2 = clock64();
-#endif
-        if (lane == 0) ans[w & (kAnsRing - 1)] = fast_ans_pack(w, 0, e, sb, ne);
-#ifdef SNAPPY_B200_STATS
-        const long long tc3 = clock64(); fs_acc[1] += (unsigned long long)(tc3 - tc2);
-#endif
-        uint32_t adv = 0;
-        e = 0;
-        if (cnt) {
-            ne = (w << 5) + E;
-            sb += cnt;
-            if (E >= 32) { adv = (E - 32) >> 5; e = E & 31u; }
+        if (ok) {
+            const uint32_t packed = e | ((v0 & 31u) << 8) | ((v1 & 31u) << 16) | ((v2 & 31u) << 24);
+            *reinterpret_cast<volatile uint32_t*>(entry + w) = packed;     // w is a multiple of 4 here
+            e = v3 & 31u;
+            w += 4;
+            slot = slot + 4 >= R ? slot + 4 - R : slot + 4;
+        } else {
+            FSTAT_T0();
+            fast_chase_steps(er, entry, nwin, R, w + 4, w, e, slot, lane FSTAT_ARG);
+            // realign to a multiple of four windows (a jump may land anywhere): the packed store needs it
+            while ((w & 3u) && w < nwin) fast_chase_steps(er, entry, nwin, R, (w + 3) & ~3u, w, e, slot, lane FSTAT_ARG);
+            FSTAT_ADD(2, lane);
         }
-        ++w; slot = nslot; row = row_next;
-        const bool adv_taken = adv != 0;
-        if (adv) {
-            for (; adv && w < nwin; --adv) {                       // windows wholly inside the copy
-                if (w >= safe) safe = fast_safe_bound(ctl, K, w, lane);
-                if (lane == 0) ans[w & (kAnsRing - 1)] = fast_ans_pack(w, 1, 0, 0, 0);
-                ++w; slot = slot + 1 == R ? 0 : slot + 1;
-            }
-            if (w < nwin) row = er[(slot << 5) + lane];
-        }
-#ifndef SB_FAST_CWIN_MASK
-#define SB_FAST_CWIN_MASK 7u
-#endif
-        if (lane == 0 && ((w & SB_FAST_CWIN_MASK) == 0 || adv_taken)) ctl->c_win = w;   // flow control only: may lag
     }
-    if (lane == 0) ctl->c_win = w;
-    if (ne < len) {                                                // trailing literal (snappy.cc:665-668)
-        if (lane == 0) seqs[sb] = seq_pack(len - ne, 0, 0);
-        ++sb;
-    }
-    return sb;
+    fast_chase_steps(er, entry, nwin, R, nwin, w, e, slot, lane FSTAT_ARG);
 }
 
 }  // namespace sb
