@@ -151,39 +151,98 @@ __device__ __forceinline__ uint32_t literal_encoded_size(uint32_t from, uint32_t
     return to > from ? literal_header_size(to - from) + (to - from) : 0u;
 }
 
-__global__ void __launch_bounds__(128) size_sparse_kernel(JobParams p) {
-    const int lane = threadIdx.x & 31;
-    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (job >= p.n_jobs) return;
+// Both kernels give one CTA to a job and one contiguous segment of the slots to each of its warps.
+// A warp walks its segment 32 slots at a time; the end of the previous copy comes from the previous
+// non-empty lane (one ballot + one shuffle: copy ends increase along the stream).  Only the literal
+// in front of a segment's FIRST copy depends on earlier segments, so a segment is summarised as
+// (position of its first copy, end of its last copy, encoded bytes without that first literal) and
+// the eight summaries are chained by a few threads.
+constexpr int kSparseWarps = kEmitThreads / 32;
+constexpr uint32_t kNoPos = 0xffffffffu;
+
+struct SparseWalk {                      // per-lane view of 32 slots
+    uint32_t v, pos, clen, off, end, before, lit, osz;
+};
+
+// before = end of the last copy in front of my slot (carry for lanes with no non-empty lane below)
+__device__ __forceinline__ void sparse_load(const uint32_t* __restrict__ q, uint32_t i, uint32_t n,
+                                            uint32_t carry, uint32_t lane, SparseWalk& k, uint32_t& nonempty) {
+    k.v = i < n ? __ldg(q + i) : 0u;
+    k.pos = sparse_pos(i, k.v); k.clen = sparse_len(k.v); k.off = sparse_off(k.v);
+    k.end = k.v ? k.pos + k.clen : 0u;
+    nonempty = __ballot_sync(kFull, k.v != 0u);
+    const uint32_t below = nonempty & ((1u << lane) - 1u);
+    const uint32_t pe = __shfl_sync(kFull, k.end, below ? 31 - __clz(below) : 0);
+    k.before = below ? pe : carry;
+}
+
+__device__ __forceinline__ void sparse_segment(uint32_t n, uint32_t warp, uint32_t& lo, uint32_t& hi) {
+    const uint32_t per = (((n + kSparseWarps - 1) / kSparseWarps) + 31u) & ~31u;
+    lo = min(n, warp * per);
+    hi = min(n, lo + per);
+}
+
+// Summary of one segment; every lane returns the same values.
+__device__ __forceinline__ void sparse_summary(const uint32_t* __restrict__ q, uint32_t n, uint32_t lo,
+                                               uint32_t hi, uint32_t lane, uint32_t& first_pos,
+                                               uint32_t& last_end, uint32_t& bytes) {
+    first_pos = kNoPos; last_end = kNoPos;
+    uint32_t sum = 0, carry = 0;
+    for (uint32_t base = lo; base < hi; base += 32) {
+        SparseWalk k;
+        uint32_t nonempty;
+        sparse_load(q, base + lane, min(n, hi), carry, lane, k, nonempty);
+        if (!nonempty) continue;
+        const uint32_t fl = __ffs(nonempty) - 1, ll = 31 - __clz(nonempty);
+        const bool seg_first = first_pos == kNoPos && lane == fl;      // its literal is added by the chain
+        if (k.v) sum += (seg_first ? 0u : literal_encoded_size(k.before, k.pos)) + copy_encoded_size(k.off, k.clen);
+        if (first_pos == kNoPos) first_pos = __shfl_sync(kFull, k.pos, fl);
+        carry = last_end = __shfl_sync(kFull, k.end, ll);
+    }
+    bytes = __reduce_add_sync(kFull, sum);
+}
+
+struct SparseChain {                     // shared: summaries in, carry-ins out
+    uint32_t first_pos[kSparseWarps], last_end[kSparseWarps], bytes[kSparseWarps];
+    uint32_t end_in[kSparseWarps + 1], out_in[kSparseWarps + 1];
+};
+
+__device__ __forceinline__ void sparse_chain(SparseChain& c, uint32_t out0) {   // one thread
+    uint32_t end = 0, out = out0;
+    for (int w = 0; w < kSparseWarps; ++w) {
+        c.end_in[w] = end; c.out_in[w] = out;
+        if (c.first_pos[w] != kNoPos) out += literal_encoded_size(end, c.first_pos[w]);
+        out += c.bytes[w];
+        if (c.last_end[w] != kNoPos) end = c.last_end[w];
+    }
+    c.end_in[kSparseWarps] = end; c.out_in[kSparseWarps] = out;
+}
+
+__global__ void __launch_bounds__(kEmitThreads) size_sparse_kernel(JobParams p) {
+    __shared__ SparseChain c;
+    const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t len = job_len_of(p, job);
     const uint32_t* q = reinterpret_cast<const uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
     const uint32_t n = sparse_slots(len);
-    uint32_t sum = 0, carry = 0;                             // carry = end of the last copy so far
-    for (uint32_t base = 0; base < n; base += 32) {
-        const uint32_t i = base + lane;
-        const uint32_t v = i < n ? q[i] : 0u;
-        const uint32_t pos = sparse_pos(i, v);
-        const uint32_t end = v ? pos + sparse_len(v) : 0u;
-        uint32_t x = end;                                    // inclusive prefix maximum of the ends
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t y = __shfl_up_sync(kFull, x, d);
-            if (lane >= d) x = max(x, y);
-        }
-        uint32_t before = __shfl_up_sync(kFull, x, 1);
-        before = lane ? max(before, carry) : carry;
-        if (v) sum += literal_encoded_size(before, pos) + copy_encoded_size(sparse_off(v), sparse_len(v));
-        carry = max(carry, __shfl_sync(kFull, x, 31));
+    uint32_t lo, hi, fp, le, by;
+    sparse_segment(n, wid, lo, hi);
+    sparse_summary(q, n, lo, hi, lane, fp, le, by);
+    if (lane == 0) { c.first_pos[wid] = fp; c.last_end[wid] = le; c.bytes[wid] = by; }
+    __syncthreads();
+    if (tid == 0) {
+        sparse_chain(c, p.with_header ? varint32_len(len) : 0u);
+        p.sizes[job] = c.out_in[kSparseWarps] + literal_encoded_size(c.end_in[kSparseWarps], len);   // + trailing literal
     }
-    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
-    sum += literal_encoded_size(carry, len);                 // trailing literal (snappy.cc:665-668)
-    if (lane == 0) p.sizes[job] = sum + (p.with_header ? varint32_len(len) : 0);
+}
+
+// warp-cooperative copy of n bytes global -> global (any alignment)
+__device__ __forceinline__ void warp_copy(uint8_t* __restrict__ d, const uint8_t* __restrict__ s, uint32_t n,
+                                          uint32_t lane) {
+    block_copy(d, s, n, lane, 32);
 }
 
 __global__ void __launch_bounds__(kEmitThreads) emit_sparse_kernel(JobParams p) {
-    __shared__ uint32_t warp_max[kEmitThreads / 32], warp_sum[kEmitThreads / 32];
-    __shared__ uint32_t carry_end_s, carry_out_s;
-    __shared__ uint32_t long_src[kMaxLong + 1], long_dst[kMaxLong + 1], long_len[kMaxLong + 1];
-    __shared__ uint32_t n_long;
+    __shared__ SparseChain c;
     const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t len = job_len_of(p, job);
     const uint8_t* __restrict__ in = p.in + (uint64_t)job * p.in_stride;
@@ -195,78 +254,63 @@ __global__ void __launch_bounds__(kEmitThreads) emit_sparse_kernel(JobParams p) 
         hdr = varint32_len(len);
         if (tid == 0) put_varint32(out, len);
     }
-    if (tid == 0) { carry_end_s = 0; carry_out_s = hdr; n_long = 0; }
+    uint32_t lo, hi, fp, le, by;
+    sparse_segment(n, wid, lo, hi);
+    sparse_summary(q, n, lo, hi, lane, fp, le, by);
+    if (lane == 0) { c.first_pos[wid] = fp; c.last_end[wid] = le; c.bytes[wid] = by; }
     __syncthreads();
-    for (uint32_t base = 0; base < n; base += kEmitThreads) {
-        const uint32_t i = base + tid;
-        const uint32_t v = i < n ? q[i] : 0u;
-        const uint32_t pos = sparse_pos(i, v), clen = sparse_len(v), off = sparse_off(v);
-        const uint32_t end = v ? pos + clen : 0u;
-        // block-wide exclusive prefix maximum of the copy ends -> start of my literal
-        uint32_t x = end;
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t y = __shfl_up_sync(kFull, x, d);
-            if (lane >= d) x = max(x, y);
-        }
-        if (lane == 31) warp_max[wid] = x;
-        __syncthreads();
-        uint32_t before = __shfl_up_sync(kFull, x, 1);
-        if (lane == 0) before = 0;
-        before = max(before, carry_end_s);
-        for (uint32_t k = 0; k < wid; ++k) before = max(before, warp_max[k]);
-        const uint32_t lit = (v && pos > before) ? pos - before : 0u;
-        const uint32_t lh = lit ? literal_header_size(lit) : 0u;
-        const uint32_t osz = v ? lh + lit + copy_encoded_size(off, clen) : 0u;
-        // block-wide exclusive prefix sum of the encoded sizes -> my output position
-        uint32_t sx = osz;
+    if (tid == 0) sparse_chain(c, hdr);
+    __syncthreads();
+    // second walk, now with the true carries: write the elements
+    uint32_t carry = c.end_in[wid], op0 = c.out_in[wid];
+    for (uint32_t base = lo; base < hi; base += 32) {
+        SparseWalk k;
+        uint32_t nonempty;
+        sparse_load(q, base + lane, min(n, hi), carry, lane, k, nonempty);
+        if (!nonempty) continue;
+        k.lit = (k.v && k.pos > k.before) ? k.pos - k.before : 0u;
+        const uint32_t lh = k.lit ? literal_header_size(k.lit) : 0u;
+        k.osz = k.v ? lh + k.lit + copy_encoded_size(k.off, k.clen) : 0u;
+        uint32_t sx = k.osz;                                  // inclusive prefix sum of the encoded sizes
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t y = __shfl_up_sync(kFull, sx, d);
-            if (lane >= d) sx += y;
+            if (lane >= (uint32_t)d) sx += y;
         }
-        if (lane == 31) warp_sum[wid] = sx;
-        __syncthreads();
-        uint32_t op = carry_out_s + sx - osz;
-        for (uint32_t k = 0; k < wid; ++k) op += warp_sum[k];
-        const uint32_t tile_end_out = op + osz;              // meaningful in the last thread
-        if (lit) {                                           // snappy.cc:337-378 EmitLiteral
-            const uint32_t m = lit - 1;
+        uint32_t op = op0 + sx - k.osz;
+        if (k.lit) {                                         // snappy.cc:337-378 EmitLiteral
+            const uint32_t m = k.lit - 1;
             if (m < 60) out[op] = (uint8_t)(m << 2);
             else if (m < 256) { out[op] = 60u << 2; out[op + 1] = (uint8_t)m; }
             else { out[op] = 61u << 2; out[op + 1] = (uint8_t)m; out[op + 2] = (uint8_t)(m >> 8); }
             op += lh;
-            if (lit <= kShortLiteral) {
-                for (uint32_t b = 0; b < lit; ++b) out[op + b] = __ldg(in + before + b);
-            } else {
-                const uint32_t slot = atomicAdd(&n_long, 1u);
-                long_src[slot] = before; long_dst[slot] = op; long_len[slot] = lit;
-            }
-            op += lit;
+            if (k.lit <= kShortLiteral)
+                for (uint32_t b = 0; b < k.lit; ++b) out[op + b] = __ldg(in + k.before + b);
         }
-        if (v) {                                             // snappy.cc:402-431 EmitCopy
-            uint32_t rem = clen;
+        const uint32_t lit_dst = op;
+        op += k.lit;
+        if (k.v) {                                           // snappy.cc:402-431 EmitCopy
+            uint32_t rem = k.clen;
             if (rem >= 12) {
-                while (rem >= 68) { op += put_copy_le64(out + op, off, 64, false); rem -= 64; }
-                if (rem > 64) { op += put_copy_le64(out + op, off, 60, false); rem -= 60; }
+                while (rem >= 68) { op += put_copy_le64(out + op, k.off, 64, false); rem -= 64; }
+                if (rem > 64) { op += put_copy_le64(out + op, k.off, 60, false); rem -= 60; }
             }
-            put_copy_le64(out + op, off, rem, rem < 12);
+            put_copy_le64(out + op, k.off, rem, rem < 12);
         }
-        __syncthreads();
-        const uint32_t nl = n_long;
-        for (uint32_t k = 0; k < nl; ++k)
-            block_copy(out + long_dst[k], in + long_src[k], long_len[k], tid, kEmitThreads);
-        __syncthreads();
-        if (tid == kEmitThreads - 1) {
-            carry_end_s = max(max(before, end), carry_end_s);
-            carry_out_s = tile_end_out;
-            n_long = 0;
+        uint32_t longs = __ballot_sync(kFull, k.lit > kShortLiteral);   // long literals: the whole warp copies
+        while (longs) {
+            const int l = __ffs(longs) - 1;
+            longs &= longs - 1;
+            warp_copy(out + __shfl_sync(kFull, lit_dst, l), in + __shfl_sync(kFull, k.before, l),
+                      __shfl_sync(kFull, k.lit, l), lane);
         }
-        __syncthreads();
+        op0 += __shfl_sync(kFull, sx, 31);
+        carry = __shfl_sync(kFull, k.end, 31 - __clz(nonempty));
     }
-    // trailing literal (snappy.cc:665-668)
-    const uint32_t from = carry_end_s;
+    // trailing literal (snappy.cc:665-668): the whole block copies it
+    const uint32_t from = c.end_in[kSparseWarps];
     if (from < len) {
         const uint32_t lit = len - from, m = lit - 1;
-        uint32_t op = carry_out_s;
+        uint32_t op = c.out_in[kSparseWarps];
         if (tid == 0) {
             if (m < 60) out[op] = (uint8_t)(m << 2);
             else if (m < 256) { out[op] = 60u << 2; out[op + 1] = (uint8_t)m; }

@@ -26,7 +26,7 @@
 // step carries neither a sequence count nor a literal start.
 //
 // The stream is a valid Snappy stream, deterministic, and defined by the sequential model
-// port_fast_compress (oracle/snappy_port.c), against which tests pin it byte for byte; its size
+// port_fast_compress kept with the test infrastructure, against which tests pin it byte for byte; its size
 // stays within 2 % of the reference's on the reference's corpora (it is smaller on text, since more
 // positions are candidates).  Copies are capped at kFastCap bytes per match.
 #pragma once
@@ -175,10 +175,28 @@ __device__ __forceinline__ void fast_table_warp(const uint8_t* s, uint32_t len, 
             }
             FSTAT_ADD(1, lane);
         }
-        if (w1 - w0 == SB_FAST_TGROUP) {      // a lone warp lives on instruction-level parallelism:
-#pragma unroll                                // the windows' loads and hashes overlap, only the
-            for (uint32_t k = 0; k < SB_FAST_TGROUP; ++k)   // table accesses keep their order
-                fast_table_window(s, len, w0 + k, table, shift, cring, rl);
+        if (w1 - w0 == SB_FAST_TGROUP) {
+            // A lone warp lives on instruction-level parallelism, and the compiler may not move one
+            // window's loads above another window's stores (all shared memory), so the group is
+            // staged by hand: every window's word and hash first, then the table accesses in window
+            // order (a store does not wait for the look-up before it), then the candidates.
+            uint32_t h[SB_FAST_TGROUP], T[SB_FAST_TGROUP];
+#pragma unroll
+            for (uint32_t k = 0; k < SB_FAST_TGROUP; ++k) h[k] = hash32(lds32u(s, ((w0 + k) << 5) + rl), shift);
+#pragma unroll
+            for (uint32_t k = 0; k < SB_FAST_TGROUP; ++k) {
+                const uint32_t pos = ((w0 + k) << 5) + rl;
+                T[k] = kNoCand;
+                if (pos + 4 <= len) {
+                    T[k] = table[h[k]];
+                    table[h[k]] = (uint16_t)pos;
+                }
+            }
+#pragma unroll
+            for (uint32_t k = 0; k < SB_FAST_TGROUP; ++k) {
+                const uint32_t w = w0 + k;
+                cring[((w & (kCandRing - 1)) << 5) + rl] = (uint16_t)((w | rl) ? T[k] : kNoCand);
+            }
         } else {
             for (uint32_t w = w0; w < w1; ++w) fast_table_window(s, len, w, table, shift, cring, rl);
         }
@@ -200,7 +218,15 @@ __device__ __forceinline__ void fast_evaluate(const uint8_t* s, uint32_t len, co
                                               int lane FSTAT_PARAM) {
     // (the record slot is free: this warp has already emitted the window that used it, w - 2K)
     FSTAT_T0();
-    for (uint32_t spins = 0; ctl->t_done <= w; ++spins) FAST_WATCHDOG(spins, "evaluator waits for candidates", w, ctl->t_done);
+#ifndef SB_FAST_TSLEEP
+#define SB_FAST_TSLEEP 40
+#endif
+    for (uint32_t spins = 0; ctl->t_done <= w; ++spins) {
+#if SB_FAST_TSLEEP > 0
+        __nanosleep(SB_FAST_TSLEEP);       // hot spinning here took 60 % of the SM's issue slots (ncu), mostly from the table warp
+#endif
+        FAST_WATCHDOG(spins, "evaluator waits for candidates", w, ctl->t_done);
+    }
     __syncwarp();
     FSTAT_ADD(2, lane);
     const uint32_t pos = (w << 5) + lane;
