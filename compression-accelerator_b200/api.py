@@ -49,6 +49,13 @@ SYMBOLS = {
                                                     C.c_int]),
     "snappy_b200_compress_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                              C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]),
+    "snappy_b200_uncompressed_length": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "snappy_b200_uncompress": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                         C.POINTER(C.c_size_t)]),
+    "snappy_b200_uncompress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                                C.c_void_p]),
+    "snappy_b200_uncompress_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                                      C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "snappy_b200_varint32": (C.c_size_t, [C.c_void_p, C.c_uint32]),
     "snappy_b200_sync": (C.c_int, [C.c_void_p]),
     "snappy_b200_host_alloc": (C.c_void_p, [C.c_size_t]),
@@ -191,6 +198,28 @@ class Context:
         _check(lib().snappy_b200_compress_batch(self._h, arr.ctypes.data, length, stride, count,
                                                 out.ctypes.data, ostride, sizes.ctypes.data, _MODES[mode]))
         return out, ostride, sizes
+
+    def uncompress(self, data: bytes) -> bytes:
+        """snappy::Uncompress (tests/swcompression.cc:49): a raw stream in, the original bytes out;
+        raises SnappyB200Error(INVALID_INPUT) for a malformed stream."""
+        n = C.c_size_t(0)
+        _check(lib().snappy_b200_uncompressed_length(data, len(data), C.byref(n)))
+        out = C.create_string_buffer(n.value + 16)
+        got = C.c_size_t(0)
+        _check(lib().snappy_b200_uncompress(self._h, data, len(data), out, n.value, C.byref(got)))
+        return out.raw[:got.value]
+
+    def uncompress_batch_device(self, src, in_stride, sizes, count, out_stride, dst=None, out_lens=None):
+        """`count` streams at src + i*in_stride (sizes[i] bytes, int32/uint32 device tensor) ->
+        (dst, out_lens): stream i decoded at dst + i*out_stride; out_lens[i] = -1 (0xffffffff) if malformed."""
+        import torch
+        if dst is None:
+            dst = torch.empty(out_stride * count, dtype=torch.uint8, device=src.device)
+        if out_lens is None:
+            out_lens = torch.zeros(count, dtype=torch.int32, device=src.device)
+        _check(lib().snappy_b200_uncompress_batch_device(self._h, src.data_ptr(), in_stride, sizes.data_ptr(),
+                                                         count, dst.data_ptr(), out_stride, out_lens.data_ptr()))
+        return dst, out_lens
 
     # ---- device tensors (torch uint8, on this context's device) -------------------------
     def compress_device(self, src, dst=None, out_n=None, mode="exact", header=True):

@@ -482,13 +482,76 @@ unsigned long snappy_b200_rocc_compress(char* source, int uncompressed_length, c
     return st == SNAPPY_B200_OK ? (unsigned long)out_n : 0ul;
 }
 
-/* tests/compression.c:32-39.  The reference hardware never implemented this command
- * (CompressionAccelerator.scala:385-388 only raises busy); until the device decompressor of
- * SURVEY.md section 8f lands it reports failure (non-zero), as the contract allows. */
+snappy_b200_status snappy_b200_uncompressed_length(const void* src, size_t n, size_t* result) {
+    if (!src || !result) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    const uint8_t* p = (const uint8_t*)src;
+    uint32_t v = 0, shift = 0;
+    for (size_t i = 0; i < n && shift <= 28; ++i, shift += 7) {
+        const uint32_t b = p[i];
+        if (shift == 28 && (b & 0x7fu) > 15u) break;
+        v |= (b & 0x7fu) << shift;
+        if (b < 128) { *result = v; return SNAPPY_B200_OK; }
+    }
+    return fail(SNAPPY_B200_INVALID_INPUT, "malformed length preamble");
+}
+
+snappy_b200_status snappy_b200_uncompress_device(snappy_b200_ctx* c, const void* d_src, size_t n,
+                                                 void* d_dst, size_t dst_cap, unsigned long long* d_out_n) {
+    if (!c || !d_src || !d_out_n || (!d_dst && dst_cap)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (n == 0 || n > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "stream length out of range");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(sb::launch_decode((const uint8_t*)d_src, 0, nullptr, (uint32_t)n, 1, (uint8_t*)d_dst, 0, dst_cap,
+                         nullptr, d_out_n, c->stream, &c->launches));
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_uncompress_batch_device(snappy_b200_ctx* c, const void* d_src,
+                                                       size_t in_stride, const uint32_t* d_sizes,
+                                                       size_t count, void* d_dst, size_t out_stride,
+                                                       uint32_t* d_out_lens) {
+    if (!c || !d_src || !d_sizes || !d_dst || !d_out_lens) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (count > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "too many streams");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(sb::launch_decode((const uint8_t*)d_src, in_stride, d_sizes, 0, (uint32_t)count, (uint8_t*)d_dst,
+                         out_stride, out_stride, d_out_lens, nullptr, c->stream, &c->launches));
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_uncompress(snappy_b200_ctx* c, const void* src, size_t n, void* dst,
+                                          size_t dst_cap, size_t* out_n) {
+    if (!src || !out_n || (!dst && dst_cap)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    size_t ulen = 0;
+    snappy_b200_status st = snappy_b200_uncompressed_length(src, n, &ulen);
+    if (st != SNAPPY_B200_OK) return st;
+    if (ulen > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < uncompressed length");
+    if (n > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "stream length out of range");
+    if (!c) { st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(c->d_in.reserve(n + 64));
+    CU(c->d_out.reserve(ulen + 64));
+    CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
+    CU(sb::launch_decode((const uint8_t*)c->d_in.p, 0, nullptr, (uint32_t)n, 1, (uint8_t*)c->d_out.p, 0, ulen,
+                         nullptr, c->d_total, c->stream, &c->launches));
+    CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (*c->h_total == ~0ull) return fail(SNAPPY_B200_INVALID_INPUT, "malformed Snappy stream");
+    const size_t got = (size_t)*c->h_total;
+    if (got) CU(cudaMemcpyAsync(dst, c->d_out.p, got, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *out_n = got;
+    return SNAPPY_B200_OK;
+}
+
+/* tests/compression.c:32-39: uncompress(source, compressed_length, dest) -> non-zero on failure.
+ * The caller sizes dest (no capacity argument in the reference contract); the stream's own length
+ * preamble says how much is written.  (The reference hardware left this command a stub,
+ * CompressionAccelerator.scala:385-388.) */
 unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, char* dest) {
-    (void)source; (void)compressed_length; (void)dest;
-    fail(SNAPPY_B200_INVALID_INPUT, "uncompress: device decompressor not built yet");
-    return 1ul;
+    if (compressed_length <= 0) { fail(SNAPPY_B200_INVALID_INPUT, "bad length"); return 1ul; }
+    size_t ulen = 0, out_n = 0;
+    if (snappy_b200_uncompressed_length(source, (size_t)compressed_length, &ulen) != SNAPPY_B200_OK) return 1ul;
+    return snappy_b200_uncompress(nullptr, source, (size_t)compressed_length, dest, ulen, &out_n) == SNAPPY_B200_OK
+               ? 0ul : 1ul;
 }
 
 }  // extern "C"

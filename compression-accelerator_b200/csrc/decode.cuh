@@ -1,0 +1,145 @@
+// decode.cuh -- Snappy raw-stream decompressor, one warp per stream.
+//
+// Behind uncompress(source, compressed_length, dest) of the reference's driver
+// (tests/compression.c:32-39; the reference hardware left the command a stub,
+// CompressionAccelerator.scala:385-388).  Follows tests/snappy/format_description.txt and the tag
+// semantics of SnappyDecompressor::DecompressAllTags (tests/snappy/snappy.cc:811-911): varint32
+// length, then literal / copy-1 / copy-2 / copy-4 elements.  Element boundaries can only be found
+// by walking the stream, so a stream is decoded by ONE warp: the walk is warp-uniform, the bytes of
+// every element are moved by all 32 lanes (overlapping copies replicate the offset-long pattern,
+// so even offset < length copies move in parallel).  Parallelism comes from many streams at once
+// (the page-shaped batch); a single large stream is decoded correctly but at one warp's pace.
+// Hardened like the reference's decompressor (snappy_unittest.cc:536-): every length and offset is
+// checked; a malformed stream yields kDecodeError, never an out-of-bounds access.
+#pragma once
+#include "kernels.h"
+#include "snappy_device.cuh"
+
+namespace sb {
+
+constexpr uint32_t kDecodeError = 0xffffffffu;
+
+struct DecodeParams {
+    const uint8_t* in;            // stream j at in + j*in_stride
+    uint64_t in_stride;
+    const uint32_t* in_sizes;     // compressed length of stream j (nullptr: every stream is in_size bytes)
+    uint32_t in_size;
+    uint32_t n_jobs;
+    uint8_t* out;                 // stream j decodes to out + j*out_stride
+    uint64_t out_stride;
+    uint64_t out_cap;             // capacity per stream
+    uint32_t* out_lens;           // decoded length of stream j, kDecodeError if malformed (may be nullptr)
+    unsigned long long* out_len64;// single-stream flavour: length or ~0ull (may be nullptr)
+};
+
+// n bytes d[0..n) = s[0..n), s read-only input (any alignment), all lanes of the warp
+__device__ __forceinline__ void decode_literal(uint8_t* __restrict__ d, const uint8_t* __restrict__ s,
+                                               uint32_t n, uint32_t lane) {
+    if (n <= 64) {
+        for (uint32_t i = lane; i < n; i += 32) d[i] = __ldg(s + i);
+        return;
+    }
+    uint32_t head = (uint32_t)((16u - ((uintptr_t)d & 15u)) & 15u);
+    if (lane < head) d[lane] = __ldg(s + lane);
+    const uint32_t body = (n - head) >> 4;
+    uint4* d4 = reinterpret_cast<uint4*>(d + head);
+    const uint8_t* sb_ = s + head;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)sb_ & ~(uintptr_t)3);
+    const uint32_t sh = ((uint32_t)(uintptr_t)sb_ & 3u) << 3;
+    for (uint32_t j = lane; j < body; j += 32) {
+        const uint32_t* q = w + (j << 2);
+        const uint32_t a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2), a3 = __ldg(q + 3);
+        const uint32_t a4 = sh ? __ldg(q + 4) : 0u;
+        uint4 v;
+        v.x = __funnelshift_r(a0, a1, sh);
+        v.y = __funnelshift_r(a1, a2, sh);
+        v.z = __funnelshift_r(a2, a3, sh);
+        v.w = __funnelshift_r(a3, a4, sh);
+        d4[j] = v;
+    }
+    const uint32_t done = head + (body << 4);
+    if (done + lane < n) d[done + lane] = __ldg(s + done + lane);
+}
+
+// n bytes at d[0..n) = the bytes `off` back, pattern-replicated when off < n (snappy.cc:744-790
+// IncrementalCopy).  Reads go to L2 (ld.cg): they fetch what this warp wrote a moment ago.
+__device__ __forceinline__ void decode_copy(uint8_t* d, uint32_t off, uint32_t n, uint32_t lane) {
+    const uint8_t* s = d - off;
+    if (off >= n) {
+        for (uint32_t i = lane; i < n; i += 32) d[i] = __ldcg(s + i);
+    } else {
+        for (uint32_t i = lane; i < n; i += 32) d[i] = __ldcg(s + (i % off));
+    }
+}
+
+__global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (job >= p.n_jobs) return;
+    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
+    const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
+    uint8_t* dst = p.out + (uint64_t)job * p.out_stride;
+    bool bad = false;
+    // varint32 preamble (snappy.cc:1006-1009 on the way in, :864- on the way out)
+    uint32_t ip = 0, ulen = 0, shift = 0;
+    for (;;) {
+        if (ip >= n || shift > 28) { bad = true; break; }
+        const uint32_t b = __ldg(src + ip++);
+        if (shift == 28 && (b & 0x7fu) > 15u) { bad = true; break; }   // would not fit 32 bits
+        ulen |= (b & 0x7fu) << shift;
+        if (b < 128) break;
+        shift += 7;
+    }
+    if (!bad && (uint64_t)ulen > p.out_cap) bad = true;
+    uint32_t op = 0;
+    while (!bad && ip < n) {
+        const uint32_t tag = __ldg(src + ip++);
+        const uint32_t kind = tag & 3u;
+        if (kind == 0) {                                         // literal
+            uint32_t len = (tag >> 2) + 1;
+            if (len > 60) {
+                const uint32_t extra = len - 60;
+                if (ip + extra > n) { bad = true; break; }
+                uint32_t v = 0;
+                for (uint32_t i = 0; i < extra; ++i) v |= (uint32_t)__ldg(src + ip + i) << (8 * i);
+                if (v == 0xffffffffu) { bad = true; break; }
+                len = v + 1;
+                ip += extra;
+            }
+            if (len > n - ip || len > ulen - op) { bad = true; break; }
+            decode_literal(dst + op, src + ip, len, lane);
+            ip += len;
+            op += len;
+        } else {                                                 // copy-1 / copy-2 / copy-4
+            uint32_t len, off;
+            if (kind == 1) {
+                if (ip + 1 > n) { bad = true; break; }
+                len = 4 + ((tag >> 2) & 7u);
+                off = ((tag >> 5) << 8) | __ldg(src + ip);
+                ip += 1;
+            } else if (kind == 2) {
+                if (ip + 2 > n) { bad = true; break; }
+                len = (tag >> 2) + 1;
+                off = __ldg(src + ip) | ((uint32_t)__ldg(src + ip + 1) << 8);
+                ip += 2;
+            } else {
+                if (ip + 4 > n) { bad = true; break; }
+                len = (tag >> 2) + 1;
+                off = __ldg(src + ip) | ((uint32_t)__ldg(src + ip + 1) << 8) |
+                      ((uint32_t)__ldg(src + ip + 2) << 16) | ((uint32_t)__ldg(src + ip + 3) << 24);
+                ip += 4;
+            }
+            if (off == 0 || off > op || len > ulen - op) { bad = true; break; }
+            decode_copy(dst + op, off, len, lane);
+            op += len;
+        }
+        __syncwarp();                                            // the next element may read these bytes
+    }
+    if (!bad && op != ulen) bad = true;
+    if (lane == 0) {
+        if (p.out_lens) p.out_lens[job] = bad ? kDecodeError : op;
+        if (p.out_len64) *p.out_len64 = bad ? ~0ull : (unsigned long long)op;
+    }
+}
+
+}  // namespace sb

@@ -16,6 +16,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "parse_pipe.cuh"
 #include "parse_fast.cuh"
 #include "emit.cuh"
+#include "decode.cuh"
 #include <type_traits>
 
 namespace sb {
@@ -392,6 +393,19 @@ cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long*
     if (p.n_jobs == 0) return cudaSuccess;
     if (p.sparse) emit_sparse_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
     else emit_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t* in_sizes, uint32_t in_size,
+                          uint32_t count, uint8_t* out, uint64_t out_stride, uint64_t out_cap,
+                          uint32_t* out_lens, unsigned long long* out_len64, cudaStream_t st,
+                          unsigned long long* launches) {
+    if (count == 0) return cudaSuccess;
+    DecodeParams p;
+    p.in = in; p.in_stride = in_stride; p.in_sizes = in_sizes; p.in_size = in_size; p.n_jobs = count;
+    p.out = out; p.out_stride = out_stride; p.out_cap = out_cap; p.out_lens = out_lens; p.out_len64 = out_len64;
+    decode_kernel<<<(count + 3) / 4, 128, 0, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -64,6 +64,14 @@ cudaError_t launch_check(const JobParams& p, unsigned long long* report, cudaStr
 // Diagnostics counters of the pipelined parser (all zero unless built with -DSNAPPY_B200_STATS).
 cudaError_t read_stats(unsigned long long* out16, bool reset);
 
+// Decompression (decode.cuh): `count` streams, stream j = in + j*in_stride with in_sizes[j] (or in_size)
+// bytes, decoded to out + j*out_stride (capacity out_cap each); out_lens[j] = decoded length or
+// 0xffffffff for a malformed stream; out_len64 (single stream) likewise with ~0.
+cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t* in_sizes, uint32_t in_size,
+                          uint32_t count, uint8_t* out, uint64_t out_stride, uint64_t out_cap,
+                          uint32_t* out_lens, unsigned long long* out_len64, cudaStream_t st,
+                          unsigned long long* launches);
+
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 
 }  // namespace sb

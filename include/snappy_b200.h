@@ -86,6 +86,26 @@ snappy_b200_status snappy_b200_compress_batch(snappy_b200_ctx* ctx, const void* 
                                               size_t in_stride, size_t count, void* dst,
                                               size_t out_stride, uint32_t* sizes, int mode);
 
+/* ---- decompression: replaces snappy::RawUncompress (snappy.cc:1338-1346) and the RoCC uncompress
+ * command (tests/compression.c:32-39).  A stream is decoded by one warp (element boundaries can
+ * only be found by walking the stream), so throughput comes from many streams per call.  Malformed
+ * input is detected, never dereferenced out of bounds (as snappy_unittest.cc:536- demands). */
+/* Parse the varint32 preamble (snappy.cc GetUncompressedLength); host memory. */
+snappy_b200_status snappy_b200_uncompressed_length(const void* src, size_t n, size_t* result);
+/* Host pointers, synchronous.  dst_cap >= the stream's uncompressed length; *out_n = bytes written.
+ * SNAPPY_B200_INVALID_INPUT for a malformed stream. */
+snappy_b200_status snappy_b200_uncompress(snappy_b200_ctx* ctx, const void* src, size_t n, void* dst,
+                                          size_t dst_cap, size_t* out_n);
+/* Device pointers, asynchronous on the context's stream: *d_out_n = length, or ~0 if malformed. */
+snappy_b200_status snappy_b200_uncompress_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
+                                                 void* d_dst, size_t dst_cap, unsigned long long* d_out_n);
+/* `count` streams: stream i = d_src + i*in_stride, d_sizes[i] bytes, decoded to d_dst + i*out_stride
+ * (capacity out_stride each); d_out_lens[i] = decoded length or 0xffffffff if malformed. */
+snappy_b200_status snappy_b200_uncompress_batch_device(snappy_b200_ctx* ctx, const void* d_src,
+                                                       size_t in_stride, const uint32_t* d_sizes,
+                                                       size_t count, void* d_dst, size_t out_stride,
+                                                       uint32_t* d_out_lens);
+
 /* Write varint32(n) at dst (host memory), return its length 1..5
  * (tests/snappy/snappy-stubs-internal.h:552-578). */
 size_t snappy_b200_varint32(void* dst, uint32_t n);

@@ -1,0 +1,103 @@
+"""Device decompressor behind uncompress(source, compressed_length, dest) (tests/compression.c:32-39).
+Round trips (streams from the reference Snappy, from our exact and fast modes), the driver contract,
+the page-shaped batch, and malformed streams in the spirit of snappy_unittest.cc:536- (truncation,
+bad offsets, length lies): rejected, never out of bounds."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import corpus
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+MAN = corpus.manifest()
+
+
+def cases():
+    yield "thistle", corpus.THISTLE
+    yield "empty", b""
+    yield "one", b"x"
+    for name in ("fox-in-socks.txt", "alice29.txt", "html", "fireworks.jpeg", "randomASCII.txt"):
+        yield name, corpus.fixture(name)
+    yield "a70000", b"a" * 70000
+    yield "abc", b"abc" * 5000
+    yield "struct", corpus.structured_random(150000, 9)
+
+
+@pytest.mark.parametrize("name,data", list(cases()), ids=[n for n, _ in cases()])
+def test_roundtrip_reference_streams(ctx, oracle, pkg, name, data):
+    comp = oracle.compress(data)                 # the reference's own stream
+    assert ctx.uncompress(comp) == data
+    assert ctx.uncompress(ctx.compress(data)) == data
+    assert ctx.uncompress(ctx.compress(data, mode="fast")) == data
+
+
+def test_rocc_driver_roundtrip(pkg):
+    """main() of tests/compression.c:41-61: compress into a 256-byte array, uncompress, compare."""
+    compressed = C.create_string_buffer(256)
+    recovered = C.create_string_buffer(256)
+    n = pkg.rocc_compress(corpus.THISTLE, 130, compressed)
+    assert n == 112
+    assert pkg.rocc_uncompress(compressed, n, recovered) == 0
+    assert recovered.raw[:130] == corpus.THISTLE
+    assert pkg.rocc_uncompress(b"\x05\xff\xff", 3, recovered) != 0        # garbage: non-zero = failure
+
+
+def test_copy4_and_long_literal_forms(ctx):
+    """Elements our compressor never emits but the format allows: copy-4 and 3/4-byte literal lengths."""
+    lit = bytes(range(256)) * 300                                # 76800 bytes
+    n = len(lit) + 10
+    hdr = bytearray()
+    v = n
+    while v >= 128:
+        hdr.append((v & 0x7f) | 0x80); v >>= 7
+    hdr.append(v)
+    L = len(lit) - 1
+    stream = bytes(hdr) + bytes([62 << 2, L & 0xff, (L >> 8) & 0xff, L >> 16]) + lit
+    stream += bytes([3 | ((10 - 1) << 2)]) + (70000).to_bytes(4, "little")   # copy-4: len 10, offset 70000
+    want = lit + lit[len(lit) - 70000:len(lit) - 70000 + 10]
+    assert ctx.uncompress(stream) == want
+
+
+def test_malformed_streams_rejected(ctx, oracle, pkg):
+    good = oracle.compress(corpus.fixture("fox-in-socks.txt"))
+    bad = [
+        b"",                                   # no preamble
+        b"\x80\x80\x80\x80\x80\x01",           # varint too long
+        good[:-1], good[:len(good) // 2],      # truncated
+        good + b"\x00",                        # trailing garbage element (1-byte literal without data / too long)
+        b"\x0a" + bytes([0x01 | (0 << 2), 0x05]),        # copy before any output (offset 5 > produced 0)
+        b"\x08\x0cabcd" + bytes([0x01, 0x00]),           # copy with offset 0
+        b"\x04\x0cabcd\x00z",                             # more output than the preamble promises
+        b"\x10\x0cabcd",                                  # less output than the preamble promises
+        b"\x05" + bytes([61 << 2, 0xff, 0xff]),           # literal longer than the input
+    ]
+    for s in bad:
+        with pytest.raises(pkg.SnappyB200Error) as ei:
+            ctx.uncompress(s)
+        assert ei.value.status == pkg.api.INVALID_INPUT if hasattr(pkg, "api") else ei.value.status == 1
+
+
+def test_batch_pages_roundtrip(ctx, oracle):
+    """Config 4 shape: 2048 pages compressed on the device, decompressed on the device, compared."""
+    import torch
+    text = corpus.fixture("all-mtg-cards.txt")
+    count = 2048
+    pages = np.frombuffer((text * 3)[:4096 * count], dtype=np.uint8).copy()
+    pages[4096 * 100:4096 * 110] = 97
+    src = torch.from_numpy(pages).cuda()
+    comp, ostride, sizes = ctx.compress_batch_device(src, 4096, 4096, count)
+    out, lens = ctx.uncompress_batch_device(comp, ostride, sizes, count, 4096)
+    ctx.sync()
+    assert (lens.cpu().numpy() == 4096).all()
+    assert bytes(out.cpu().numpy()) == pages.tobytes()
+    # one corrupted page is flagged, the others are unaffected
+    comp2 = comp.clone()
+    comp2[ostride * 7 + 3] = 0xff
+    comp2[ostride * 7 + 4] = 0xff
+    out2, lens2 = ctx.uncompress_batch_device(comp2, ostride, sizes, count, 4096)
+    ctx.sync()
+    l2 = lens2.cpu().numpy()
+    assert l2[7] == -1 or l2[7] == 4096          # 0xffffffff, unless the damage happened to stay decodable
+    assert (np.delete(l2, 7) == 4096).all()
