@@ -89,7 +89,7 @@ template <bool kGlobal> struct PipeCfg;
 #define SB_PIPE_P 4
 #endif
 #ifndef SB_PIPE_LEAD
-#define SB_PIPE_LEAD 3
+#define SB_PIPE_LEAD 2
 #endif
 template <> struct PipeCfg<false> { static constexpr uint32_t P = 2, R = 8, LEAD = 3; };
 template <> struct PipeCfg<true>  { static constexpr uint32_t P = SB_PIPE_P, R = 8, LEAD = SB_PIPE_LEAD; };
@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
         if (len >= kMargin) {
             pr.src = in_src; pr.len = len; pr.ip_limit = len - kMargin;
             pr.table = table; pr.ps = ps; pr.shift = shift;
+            pr.table_s = (uint32_t)__cvta_generic_to_shared(table);
             pr.run();
         }
         __syncwarp();

@@ -24,6 +24,9 @@
 namespace sb {
 
 constexpr uint32_t kDone = 0xffffffffu;
+#ifndef SB_PIPE_EARLY
+#define SB_PIPE_EARLY 2                  // the speculative look-up may run this many windows ahead of the final one
+#endif
 #ifndef SB_PIPE_SLEEP
 #define SB_PIPE_SLEEP 100
 #endif
@@ -165,33 +168,22 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
     const uint32_t ip_limit = len - kMargin;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t next = p, parity = 0;
-    for (uint32_t idle = 0;;) {
-        const uint32_t cw = ps->cur_win;
-        if (cw == kDone) return;
-        if (next < cw) next = cw + (p + P - cw % P) % P;
-        if (next >= cw + LEAD || next >= nwin) {
-            // far enough ahead (or nothing left): sleep in hardware until the resolver moves on.  The
-            // parity is only a belief; a completed phase returns at once and flips it.
-            if (mbar_try_wait(&ps->bar, parity)) parity ^= 1u;
-#if SB_PIPE_SLEEP > 0
-            else __nanosleep(SB_PIPE_SLEEP);                 // try_wait times out quickly: do not burn issue slots
-#endif
-            if (++idle > (1u << 24)) __trap();               // watchdog: never hang the GPU
-            continue;
-        }
-        idle = 0;
-        const uint32_t w = next, si = w % R;
-        const uint32_t pos = (w << 5) + lane;
-        const bool valid = pos < ip_limit;
-        uint32_t d0 = 0, d1 = 0, d2 = 0, d3 = 0;
-        if (valid) src.ld16(pos, d0, d1, d2, d3);
-        const uint32_t h = hash32(d0, shift);
-        const uint32_t T = table[h];                         // speculative: may miss pending inserts
-        uint32_t c0 = ~d0, c1 = 0, c2 = 0, c3 = 0;
-        if (valid) src.ld16(T, c0, c1, c2, c3);
-        const bool hit = (c0 == d0);
+    // A window is produced in three phases so that the table look-up the record is built on happens
+    // as late as possible (fewer pending inserts missed) without the global-memory latency behind it:
+    //   A   (any time)           own 16 bytes per lane, hash, same-hash lanes -- table-independent
+    //   B1  (w < cur_win+LEAD_A)  speculative look-up, candidate bytes, 4-byte compare, pre-extension
+    //   B2  (w < cur_win+LEAD)    look-up again; only lanes whose entry moved since B1 redo their
+    //                             candidate (usually none: no memory latency), then publish.
+    constexpr uint32_t LEAD_A = LEAD + SB_PIPE_EARLY;
+    uint32_t have = kDone, have_b1 = kDone;
+    uint32_t d0 = 0, d1 = 0, d2 = 0, d3 = 0, h = 0, ph = 0, inval = 0, T = 0, ml = 0;
+    bool hit = false;
+    auto evaluate = [&](uint32_t pos, uint32_t cand) {       // compare + pre-extend against one candidate
+        uint32_t c0, c1, c2, c3;
+        src.ld16(cand, c0, c1, c2, c3);
+        hit = (c0 == d0);
         const uint32_t x1 = c1 ^ d1, x2 = c2 ^ d2, x3 = c3 ^ d3;
-        uint32_t ml = 12;
+        ml = 12;
         if (x3) ml = 8 + ((uint32_t)(__ffs(x3) - 1) >> 3);
         if (x2) ml = 4 + ((uint32_t)(__ffs(x2) - 1) >> 3);
         if (x1) ml = (uint32_t)(__ffs(x1) - 1) >> 3;
@@ -200,7 +192,7 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
             for (uint32_t o = 16; o < 80 && pos + o + 16 <= len; o += 16) {
                 uint32_t e0, e1, e2, e3, g0, g1, g2, g3;
                 src.ld16(pos + o, e0, e1, e2, e3);
-                src.ld16(T + o, g0, g1, g2, g3);
+                src.ld16(cand + o, g0, g1, g2, g3);
                 const uint32_t y0 = e0 ^ g0, y1 = e1 ^ g1, y2 = e2 ^ g2, y3 = e3 ^ g3;
                 if (y0 | y1 | y2 | y3) {
                     uint32_t q = 12 + ((uint32_t)(__ffs(y3) - 1) >> 3);
@@ -212,9 +204,44 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
                 }
             }
         }
-        const uint32_t ph = __match_any_sync(kFull, h);
+    };
+    for (uint32_t idle = 0;;) {
+        const uint32_t cw = ps->cur_win;
+        if (cw == kDone) return;
+        if (next < cw) next = cw + (p + P - cw % P) % P;
+        if (next < nwin && have != next) {                   // ---- phase A
+            have = next;
+            d0 = d1 = d2 = d3 = 0;
+            const bool v = (next << 5) + lane < ip_limit;
+            if (v) src.ld16((next << 5) + lane, d0, d1, d2, d3);
+            h = hash32(d0, shift);
+            ph = __match_any_sync(kFull, h);                 // slow instruction: keep it off the late phase
+            inval = ~__ballot_sync(kFull, v);
+        }
+        if (next < nwin && have_b1 != next && next < cw + LEAD_A) {   // ---- phase B1
+            have_b1 = next;
+            T = table[h];                                    // speculative: may miss pending inserts
+            hit = false; ml = 0;
+            if ((next << 5) + lane < ip_limit) evaluate((next << 5) + lane, T);
+        }
+        if (next >= cw + LEAD || next >= nwin) {
+            // far enough ahead (or nothing left): sleep in hardware until the resolver moves on.  The
+            // parity is only a belief; a completed phase returns at once and flips it.
+            if (mbar_try_wait(&ps->bar, parity)) parity ^= 1u;
+#if SB_PIPE_SLEEP > 0
+            else __nanosleep(SB_PIPE_SLEEP);                 // try_wait times out quickly: do not burn issue slots
+#endif
+            if (++idle > (1u << 24)) __trap();               // watchdog: never hang the GPU
+            continue;
+        }
+        idle = 0;
+        const uint32_t w = next, si = w % R;                 // ---- phase B2 (have_b1 == w: LEAD <= LEAD_A)
+        const uint32_t pos = (w << 5) + lane;
+        {
+            const uint32_t T2 = table[h];
+            if (pos < ip_limit && T2 != T) { T = T2; evaluate(pos, T); }
+        }
         const bool peer = (ph & lt) != 0;
-        const uint32_t inval = ~__ballot_sync(kFull, valid);
         const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
         const uint32_t L = __ballot_sync(kFull, hit || peer) & lanes_below(vpre_end);
         const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == kLongMatch);
@@ -235,6 +262,7 @@ struct PipeResolver {
     Src src;
     uint32_t len, ip_limit;
     uint16_t* table;
+    uint32_t table_s;                    // the table's address in the shared window
     PipeShared<R>* ps;
     int shift, lane;
     seq_t* seqs;
@@ -245,9 +273,10 @@ struct PipeResolver {
     uint32_t st_win = 0, st_stale = 0, st_nslow = 0, st_serial = 0, st_slowhit = 0, st_cstale = 0, st_cpeer = 0;
 
     // Write the window's pending inserts: per hash slot the highest inserted lane wins (serial order).
-    __device__ __forceinline__ void commit(uint16_t* tbl, uint32_t h, uint32_t pos, uint32_t I, uint32_t ph) {
+    __device__ __forceinline__ void commit(uint16_t*, uint32_t h, uint32_t pos, uint32_t I, uint32_t ph) {
         const uint32_t gt = ~((2u << lane) - 1u);
-        if (((I >> lane) & 1u) && (ph & I & gt) == 0) tbl[h] = (uint16_t)pos;
+        if (((I >> lane) & 1u) && (ph & I & gt) == 0)
+            asm volatile("st.shared.u16 [%0], %1;" :: "r"(table_s + (h << 1)), "h"((uint16_t)pos) : "memory");
         __syncwarp();
     }
 
@@ -275,7 +304,12 @@ struct PipeResolver {
             const uint4 rec = ps->rec[si][lane];
             const uint4 hdr = ps->hdr[si];
             const uint32_t h = rec.x & 0xffffu;
-            const uint32_t T = table[h];                     // exact: earlier windows are committed
+            uint32_t T;                                      // exact: earlier windows are committed
+            {
+                uint16_t t16;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t16) : "r"(table_s + (h << 1)) : "memory");
+                T = t16;
+            }
             uint32_t L = hdr.x, SLOWM = hdr.y, nxek = rec.y;
             const uint32_t inval = hdr.z, ph = rec.z;
             const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;

@@ -36,8 +36,9 @@ __device__ __forceinline__ void lds16u(const uint8_t* s, uint32_t pos, uint32_t&
     b3 = __funnelshift_r(a3, a4, sh);
 }
 
-__device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return s >= 32 ? 0u : (kFull << s); }
-__device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return e >= 32 ? kFull : ((1u << e) - 1u); }
+// one SHF each: the funnel shift clamps the count at 32
+__device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return __funnelshift_lc(0u, kFull, s); }
+__device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return __funnelshift_lc(kFull, 0u, e); }
 
 // Write the pending inserts `I` of a window: table[h] = pos for every inserted lane, the highest
 // lane of a hash slot winning.  Without peers in the window no two lanes share a slot.
