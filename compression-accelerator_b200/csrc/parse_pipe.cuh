@@ -142,7 +142,7 @@ constexpr uint32_t kLongMatch = 127;     // pre-extension gave up: evaluate exac
 template <uint32_t R>
 struct alignas(16) PipeShared {
     uint4 hdr[R];                        // x = L, y = SLOWM, z = inval, w = any_peer (see parse_window.cuh)
-    uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = ph (lanes with my hash), w = (4+ml)<<17 | peer<<31
+    uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = ph (lanes with my hash), w = chain summary (lanes taken when the fast path enters at this lane)
     volatile uint32_t ready[R];          // window index + 1 whose record is complete
     volatile uint32_t cur_win;           // resolver's current window, kDone when the parse ended
     uint64_t bar;                        // mbarrier (count 1): the resolver arrives whenever cur_win moves
@@ -248,7 +248,15 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
         const uint32_t anyp = __ballot_sync(kFull, peer);
         const uint32_t ek = lane + 4 + (ml == kLongMatch ? 12u : ml);
         const uint32_t nx = lane_next(pos, ek, ip_limit, L, SLOWM);
-        ps->rec[si][lane] = make_uint4(h | (T << 16), nx | (ek << 16), ph, ((ek - lane) << 17) | ((uint32_t)peer << 31));
+        // chain summary: the lanes whose copies are taken when the parse enters the window's fast
+        // path at this lane (pointer jumping over nx; a chain has at most 8 copies)
+        uint32_t chain = 1u << lane, ptr = nx < 32 ? nx : (uint32_t)lane;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            chain |= __shfl_sync(kFull, chain, ptr);
+            ptr = __shfl_sync(kFull, ptr, ptr);
+        }
+        ps->rec[si][lane] = make_uint4(h | (T << 16), nx | (ek << 16), ph, chain);
         if (lane == 0) ps->hdr[si] = make_uint4(L, SLOWM, inval, anyp);
         __threadfence_block();
         __syncwarp();
@@ -336,12 +344,24 @@ struct PipeResolver {
 #ifdef SNAPPY_B200_STATS
                 const long long t_c0 = clock64();
 #endif
-                while (f < 32) {                              // one shuffle per copy
-                    chosen |= 1u << f;
-                    if ((uint32_t)lane == f) mylit = pos - cur_emit;
-                    const uint32_t v = __shfl_sync(kFull, nxek, f);
-                    cur_emit = wbase + (v >> 16);
-                    f = v & 0x1ffu;
+                if (!stale) {
+                    if (f < 32) {                             // the producer's chain summary holds
+                        chosen = __shfl_sync(kFull, rec.w, f);
+                        const uint32_t below = chosen & lt;
+                        const uint32_t v = __shfl_sync(kFull, nxek, 31u - __clz(chosen));
+                        const uint32_t pe = __shfl_sync(kFull, nxek, below ? 31u - __clz(below) : 0u) >> 16;
+                        mylit = pos - (below ? wbase + pe : cur_emit);
+                        cur_emit = wbase + (v >> 16);
+                        f = v & 0x1ffu;
+                    }
+                } else {
+                    while (f < 32) {                          // one shuffle per copy
+                        chosen |= 1u << f;
+                        if ((uint32_t)lane == f) mylit = pos - cur_emit;
+                        const uint32_t v = __shfl_sync(kFull, nxek, f);
+                        cur_emit = wbase + (v >> 16);
+                        f = v & 0x1ffu;
+                    }
                 }
 #ifdef SNAPPY_B200_STATS
                 const long long t_b0 = clock64(); st_pc += t_b0 - t_c0;
@@ -353,7 +373,7 @@ struct PipeResolver {
                 uint32_t e_last = 0;
                 if (chosen) {
                     if ((chosen >> lane) & 1u) {
-                        const uint2 q = make_uint2((rec.w & 0x7fffffffu) | mylit, (pos - T) << 1);
+                        const uint2 q = make_uint2(((ek - lane) << 17) | mylit, (pos - T) << 1);
                         *reinterpret_cast<uint2*>(seqs + nseq + __popc(chosen & lt)) = q;
                     }
                     nseq += __popc(chosen);
@@ -399,7 +419,7 @@ struct PipeResolver {
                     const uint32_t fs = f & 31u;
 #ifdef SNAPPY_B200_STATS
                     ++st_nslow; const long long t1 = clock64();
-                    if ((stale >> fs) & 1u) ++st_cstale; else if (__shfl_sync(kFull, rec.w, fs) >> 31) ++st_cpeer;
+                    if ((stale >> fs) & 1u) ++st_cstale; else if (__shfl_sync(kFull, ph & lt, fs)) ++st_cpeer;
 #endif
                     I |= lanes_from(sl) & lanes_below(fs) & ~SK;
                     const uint32_t pk = __shfl_sync(kFull, ph, fs) & I & lanes_below(fs);   // inserted peers
