@@ -147,7 +147,11 @@ class Context:
             lib().snappy_b200_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except TypeError:            # interpreter shutdown: module globals are already gone
+            pass
 
     @property
     def stream(self) -> int:

@@ -72,13 +72,9 @@ __device__ __forceinline__ void decode_copy(uint8_t* d, uint32_t off, uint32_t n
     }
 }
 
-__global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (job >= p.n_jobs) return;
-    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
-    const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
-    uint8_t* dst = p.out + (uint64_t)job * p.out_stride;
+// One stream, input and output in global memory.  Returns the decoded length or kDecodeError.
+__device__ __forceinline__ uint32_t decode_stream_global(const uint8_t* __restrict__ src, uint32_t n,
+                                                         uint8_t* dst, uint64_t out_cap, uint32_t lane) {
     bool bad = false;
     // varint32 preamble (snappy.cc:1006-1009 on the way in, :864- on the way out)
     uint32_t ip = 0, ulen = 0, shift = 0;
@@ -90,7 +86,7 @@ __global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
         if (b < 128) break;
         shift += 7;
     }
-    if (!bad && (uint64_t)ulen > p.out_cap) bad = true;
+    if (!bad && (uint64_t)ulen > out_cap) bad = true;
     uint32_t op = 0;
     while (!bad && ip < n) {
         const uint32_t tag = __ldg(src + ip++);
@@ -136,9 +132,146 @@ __global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
         __syncwarp();                                            // the next element may read these bytes
     }
     if (!bad && op != ulen) bad = true;
+    return bad ? kDecodeError : op;
+}
+
+__global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (job >= p.n_jobs) return;
+    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
+    const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
+    uint8_t* dst = p.out + (uint64_t)job * p.out_stride;
+    const uint32_t got = decode_stream_global(src, n, dst, p.out_cap, lane);
     if (lane == 0) {
-        if (p.out_lens) p.out_lens[job] = bad ? kDecodeError : op;
-        if (p.out_len64) *p.out_len64 = bad ? ~0ull : (unsigned long long)op;
+        if (p.out_lens) p.out_lens[job] = got;
+        if (p.out_len64) *p.out_len64 = got == kDecodeError ? ~0ull : (unsigned long long)got;
+    }
+}
+
+// ---- page-sized streams: input and output staged in shared memory ------------------------------
+// A copy element reads bytes this warp wrote a moment ago; from global memory that is an L2 round
+// trip per element on the walk's critical path.  For streams that fit (the page-shaped batch of
+// benchmark/hw_results.csv) the warp keeps its compressed input AND its output in shared memory:
+// every element costs shared-memory latency, and global memory sees one coalesced read of the
+// stream and one coalesced write of the page.  Streams that do not fit the staging area take
+// decode_stream_global.
+constexpr uint32_t kStageWarps = 4;
+constexpr uint32_t kStageOutMax = 8192;          // largest decoded size the staged kernel is launched for
+
+// unaligned 4 bytes from shared memory (the staging areas are padded: reading 3 bytes past is safe)
+__device__ __forceinline__ uint32_t stage_ld32(const uint8_t* s, uint32_t pos) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(s) + (pos >> 2);
+    return __funnelshift_r(w[0], w[1], (pos & 3u) << 3);
+}
+
+__global__ void __launch_bounds__(32 * kStageWarps) decode_staged_kernel(DecodeParams p, uint32_t stage_in,
+                                                                         uint32_t stage_out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t job = blockIdx.x * kStageWarps + wid;
+    if (job >= p.n_jobs) return;
+    uint8_t* s_in = smem + (size_t)wid * (stage_in + stage_out);
+    uint8_t* s_out = s_in + stage_in;
+    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
+    const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
+    uint8_t* dst = p.out + (uint64_t)job * p.out_stride;
+    uint32_t got;
+    const uint32_t skew = (uint32_t)((uintptr_t)src & 15u);
+    if (n == 0 || (uint64_t)skew + n + 20 > stage_in) {
+        got = n ? decode_stream_global(src, n, dst, p.out_cap, lane) : kDecodeError;
+    } else {
+        // stage the stream: whole aligned 16-byte words (a word holding one valid byte lies in a valid page)
+        {
+            const uint4* g = reinterpret_cast<const uint4*>(src - skew);
+            uint4* d = reinterpret_cast<uint4*>(s_in);
+            const uint32_t words = (skew + n + 15) >> 4;
+            for (uint32_t i = lane; i < words; i += 32) d[i] = __ldg(g + i);
+        }
+        __syncwarp();
+        const uint8_t* in = s_in + skew;                 // in[0..n) is the stream
+        bool bad = false;
+        uint32_t ip = 0, ulen = 0, shift = 0;
+        for (;;) {                                       // varint32 preamble
+            if (ip >= n || shift > 28) { bad = true; break; }
+            const uint32_t b = in[ip++];
+            if (shift == 28 && (b & 0x7fu) > 15u) { bad = true; break; }
+            ulen |= (b & 0x7fu) << shift;
+            if (b < 128) break;
+            shift += 7;
+        }
+        if (!bad && ((uint64_t)ulen > p.out_cap || ulen > stage_out)) {
+            // cannot be staged (or does not fit the caller's buffer: the global walk reports that)
+            got = decode_stream_global(src, n, dst, p.out_cap, lane);
+        } else {
+            uint32_t op = 0;
+            while (!bad && ip < n) {
+                const uint32_t w = stage_ld32(s_in, skew + ip);      // tag + up to 3 following bytes
+                const uint32_t tag = w & 0xffu, kind = tag & 3u;
+                ++ip;
+                if (kind == 0) {                                     // literal
+                    uint32_t len = (tag >> 2) + 1;
+                    if (len > 60) {
+                        const uint32_t extra = len - 60;
+                        if (ip + extra > n) { bad = true; break; }
+                        const uint32_t v = extra == 4 ? stage_ld32(s_in, skew + ip)
+                                                      : (w >> 8) & (0xffffffu >> (8 * (3 - extra)));
+                        if (v == 0xffffffffu) { bad = true; break; }
+                        len = v + 1;
+                        ip += extra;
+                    }
+                    if (len > n - ip || len > ulen - op) { bad = true; break; }
+                    for (uint32_t i = lane; i < len; i += 32) s_out[op + i] = in[ip + i];
+                    ip += len;
+                    op += len;
+                } else {                                             // copy-1 / copy-2 / copy-4
+                    uint32_t len, off;
+                    if (kind == 1) {
+                        if (ip + 1 > n) { bad = true; break; }
+                        len = 4 + ((tag >> 2) & 7u);
+                        off = ((tag >> 5) << 8) | ((w >> 8) & 0xffu);
+                        ip += 1;
+                    } else if (kind == 2) {
+                        if (ip + 2 > n) { bad = true; break; }
+                        len = (tag >> 2) + 1;
+                        off = (w >> 8) & 0xffffu;
+                        ip += 2;
+                    } else {
+                        if (ip + 4 > n) { bad = true; break; }
+                        len = (tag >> 2) + 1;
+                        off = stage_ld32(s_in, skew + ip);
+                        ip += 4;
+                    }
+                    if (off == 0 || off > op || len > ulen - op) { bad = true; break; }
+                    const uint8_t* from = s_out + op - off;          // all source bytes precede op
+                    if (off >= len) {
+                        for (uint32_t i = lane; i < len; i += 32) s_out[op + i] = from[i];
+                    } else {
+                        for (uint32_t i = lane; i < len; i += 32) s_out[op + i] = from[i % off];
+                    }
+                    op += len;
+                }
+                __syncwarp();                                        // the next element may read these bytes
+            }
+            if (!bad && op != ulen) bad = true;
+            got = bad ? kDecodeError : op;
+            if (!bad) {                                              // one coalesced write of the page
+                __syncwarp();
+                if (((uintptr_t)dst & 15u) == 0) {
+                    const uint4* s4 = reinterpret_cast<const uint4*>(s_out);
+                    uint4* d4 = reinterpret_cast<uint4*>(dst);
+                    const uint32_t words = op >> 4;
+                    for (uint32_t i = lane; i < words; i += 32) d4[i] = s4[i];
+                    for (uint32_t i = (words << 4) + lane; i < op; i += 32) dst[i] = s_out[i];
+                } else {
+                    for (uint32_t i = lane; i < op; i += 32) dst[i] = s_out[i];
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        if (p.out_lens) p.out_lens[job] = got;
+        if (p.out_len64) *p.out_len64 = got == kDecodeError ? ~0ull : (unsigned long long)got;
     }
 }
 

@@ -362,8 +362,11 @@ cudaError_t kernels_init() {
     e = cudaFuncSetAttribute(parse_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)pipe_smem_bytes<true>(kBlock));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(parse_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)fast_layout(kBlock).total);
+    e = cudaFuncSetAttribute(parse_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)fast_layout(kBlock).total);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(decode_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(kStageWarps * (3 * kStageOutMax + 128)));
 }
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
@@ -406,7 +409,16 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
     DecodeParams p;
     p.in = in; p.in_stride = in_stride; p.in_sizes = in_sizes; p.in_size = in_size; p.n_jobs = count;
     p.out = out; p.out_stride = out_stride; p.out_cap = out_cap; p.out_lens = out_lens; p.out_len64 = out_len64;
-    decode_kernel<<<(count + 3) / 4, 128, 0, st>>>(p);
+    // page-shaped batches: stage stream and page in shared memory (decode.cuh)
+    const uint64_t in_bound = in_sizes ? in_stride : (uint64_t)in_size;
+    if (count >= kStageWarps && out_cap <= kStageOutMax && in_bound <= 2 * kStageOutMax) {
+        const uint32_t stage_out = (uint32_t)((out_cap + 15) & ~15ull) + 16;
+        const uint32_t stage_in = (uint32_t)((in_bound + 15) & ~15ull) + 48;
+        const size_t smem = (size_t)kStageWarps * (stage_in + stage_out);
+        decode_staged_kernel<<<(count + kStageWarps - 1) / kStageWarps, 32 * kStageWarps, smem, st>>>(p, stage_in, stage_out);
+    } else {
+        decode_kernel<<<(count + 3) / 4, 128, 0, st>>>(p);
+    }
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--data", default="mtg", choices=["mtg", "random", "zeros", "alice"])
     ap.add_argument("--batch", type=int, default=0, help="if >0: batch path with buffers of this many bytes")
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--decode", action="store_true", help="batch path: also time the device decompressor")
     a = ap.parse_args()
     import numpy as np
     import torch
@@ -43,6 +44,19 @@ def main():
             ms = ctx.stage_ms(0)
             print("batch %d x %d B: parse %.3f ms  %.2f GB/s in, out/in %.4f" % (
                 count, a.batch, ms, count * a.batch / ms / 1e6, float(sizes.sum().item()) / (count * a.batch)))
+        if a.decode:
+            import time
+            back, lens = ctx.uncompress_batch_device(dst, ostride, sizes, count, a.batch)
+            ctx.sync()
+            t0 = time.perf_counter()
+            for _ in range(a.reps):
+                ctx.uncompress_batch_device(dst, ostride, sizes, count, a.batch, dst=back, out_lens=lens)
+            ctx.sync()
+            ms = (time.perf_counter() - t0) / a.reps * 1e3
+            comp = float(sizes.sum().item())
+            print("decode %d x %d B: %.3f ms  %.2f GB/s out, %.2f GB/s in+out; identical: %s" % (
+                count, a.batch, ms, count * a.batch / ms / 1e6, (count * a.batch + comp) / ms / 1e6,
+                bool(torch.equal(back[:count * a.batch], src[:count * a.batch])) and bool((lens == a.batch).all())))
         return
     for _ in range(a.reps):
         dst, out_n = ctx.compress_device(src, mode=a.mode)
