@@ -56,6 +56,18 @@ SYMBOLS = {
                                                 C.c_void_p]),
     "snappy_b200_uncompress_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                                       C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
+    # Snappy framing format (tests/snappy/framing_format.txt)
+    "snappy_b200_frame_max_length": (C.c_size_t, [C.c_size_t]),
+    "snappy_b200_frame_compress": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                             C.POINTER(C.c_size_t), C.c_int]),
+    "snappy_b200_frame_uncompress": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                               C.POINTER(C.c_size_t)]),
+    "snappy_b200_frame_uncompressed_length": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "snappy_b200_frame_compress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                                    C.c_size_t, C.c_void_p, C.c_int]),
+    "snappy_b200_frame_uncompress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                                      C.c_size_t, C.POINTER(C.c_size_t)]),
+    "snappy_b200_crc32c_chunks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]),
     "snappy_b200_varint32": (C.c_size_t, [C.c_void_p, C.c_uint32]),
     "snappy_b200_sync": (C.c_int, [C.c_void_p]),
     "snappy_b200_host_alloc": (C.c_void_p, [C.c_size_t]),
@@ -224,6 +236,57 @@ class Context:
         _check(lib().snappy_b200_uncompress_batch_device(self._h, src.data_ptr(), in_stride, sizes.data_ptr(),
                                                          count, dst.data_ptr(), out_stride, out_lens.data_ptr()))
         return dst, out_lens
+
+    # ---- Snappy framing format (tests/snappy/framing_format.txt) ------------------------
+    def frame_compress(self, data, mode="exact") -> bytes:
+        """Framed stream (stream identifier + CRC-checked chunks of 65,536 bytes) of `data`."""
+        n = len(data)
+        cap = lib().snappy_b200_frame_max_length(n)
+        out = C.create_string_buffer(cap + 16)
+        got = C.c_size_t(0)
+        _check(lib().snappy_b200_frame_compress(self._h, _addr(data) if n else None, n, out, cap,
+                                                C.byref(got), _MODES[mode]))
+        return out.raw[:got.value]
+
+    def frame_uncompress(self, data) -> bytes:
+        n = len(data)
+        ulen = C.c_size_t(0)
+        _check(lib().snappy_b200_frame_uncompressed_length(_addr(data), n, C.byref(ulen)))
+        out = C.create_string_buffer(ulen.value + 16)
+        got = C.c_size_t(0)
+        _check(lib().snappy_b200_frame_uncompress(self._h, _addr(data), n, out, ulen.value, C.byref(got)))
+        return out.raw[:got.value]
+
+    def frame_compress_device(self, src, dst=None, out_n=None, mode="exact"):
+        """Device tensors; asynchronous.  Returns (dst, out_n) like compress_device."""
+        import torch
+        n = src.numel()
+        cap = lib().snappy_b200_frame_max_length(n)
+        if dst is None:
+            dst = torch.empty(cap, dtype=torch.uint8, device=src.device)
+        if out_n is None:
+            out_n = torch.zeros(1, dtype=torch.int64, device=src.device)
+        _check(lib().snappy_b200_frame_compress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
+                                                       out_n.data_ptr(), _MODES[mode]))
+        return dst, out_n
+
+    def frame_uncompress_device(self, src, n, dst):
+        """Decode the n-byte framed stream in device tensor `src` into `dst`; synchronous (every
+        chunk's CRC is checked).  Returns the number of bytes written."""
+        got = C.c_size_t(0)
+        _check(lib().snappy_b200_frame_uncompress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
+                                                         C.byref(got)))
+        return got.value
+
+    def crc32c_chunks_device(self, src, chunk_len=65536, out=None):
+        """Masked CRC-32C of consecutive chunk_len-byte chunks of a device tensor -> int32 device tensor."""
+        import torch
+        n = src.numel()
+        chunks = (n + chunk_len - 1) // chunk_len
+        if out is None:
+            out = torch.zeros(max(chunks, 1), dtype=torch.int32, device=src.device)
+        _check(lib().snappy_b200_crc32c_chunks_device(self._h, src.data_ptr(), n, chunk_len, out.data_ptr()))
+        return out[:chunks]
 
     # ---- device tensors (torch uint8, on this context's device) -------------------------
     def compress_device(self, src, dst=None, out_n=None, mode="exact", header=True):

@@ -52,6 +52,7 @@ struct snappy_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     DevBuf seqs, nseq, sizes, offsets, d_in, d_out;
+    DevBuf crcs, frame_ix, frame_res;          // framing: per-chunk CRCs, chunk index, walk result + flag
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -96,16 +97,18 @@ snappy_b200_status default_ctx(snappy_b200_ctx** out) {
 // Stream / fragment-range compression with input and output on the device.
 snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst,
                                 size_t dst_cap, unsigned long long* d_out_n, int mode,
-                                bool with_header) {
+                                int framing /* 0 fragments only, 1 raw stream, 2 framed stream */) {
+    const bool with_header = framing == 1, framed = framing == 2;
     if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
     if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */ &&
         mode != 3 /* exact, single-warp window parser */ && mode != 4 /* exact, pipelined, input in smem */)
         return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
-    if (dst_cap < snappy_b200_max_compressed_length(n) - (with_header ? 0 : 0))
-        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");
+    if (dst_cap < (framed ? snappy_b200_frame_max_length(n) : snappy_b200_max_compressed_length(n)))
+        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max length of the output");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
-    const uint32_t hdr = with_header ? sb::varint32_len((uint32_t)n) : 0;
+    const uint32_t hdr = framed ? 10u : with_header ? sb::varint32_len((uint32_t)n) : 0;
+    if (framed) CU(c->crcs.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
     CU(c->seqs.reserve((size_t)n_frag * sb::seq_stride(sb::kBlock) * sizeof(sb::seq_t) + 256));
     CU(c->nseq.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
     CU(c->sizes.reserve((size_t)(n_frag + 1) * sizeof(uint32_t)));
@@ -119,9 +122,11 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.seqs = (sb::seq_t*)c->seqs.p;
     p.nseq = (uint32_t*)c->nseq.p;
     p.sizes = (uint32_t*)c->sizes.p;
-    p.with_header = 0;
+    // framed: every 64 KiB chunk is its own Snappy stream (varint preamble) behind an 8-byte chunk
+    // header + CRC, so the stream is emitted 8 bytes into the chunk's slot (frame.cuh)
+    p.with_header = framed ? 1 : 0;
     p.sparse = (mode == SNAPPY_B200_FAST);
-    p.out = (uint8_t*)d_dst;
+    p.out = (uint8_t*)d_dst + (framed ? 8 : 0);
     p.out_stride = 0;
     p.offsets = (const unsigned long long*)c->offsets.p;
     CU(cudaEventRecord(c->evp0, c->stream));
@@ -129,9 +134,18 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(sb::launch_size(p, c->stream, &c->launches));
+    if (framed) {
+        CU(sb::launch_frame_bump((uint32_t*)c->sizes.p, n_frag, c->stream, &c->launches));
+        CU(sb::launch_crc32c_chunks((const uint8_t*)d_src, nullptr, nullptr, sb::kBlock, n, sb::kBlock, n_frag,
+                                    (uint32_t*)c->crcs.p, c->stream, &c->launches));
+    }
     CU(sb::launch_scan((const uint32_t*)c->sizes.p, n_frag, (unsigned long long*)c->offsets.p, hdr,
-                       (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
+                       framed ? 0u : (uint32_t)n, (uint8_t*)d_dst, d_out_n, c->stream, &c->launches));
     CU(sb::launch_emit(p, c->stream, &c->launches));
+    if (framed)
+        CU(sb::launch_frame_headers((uint8_t*)d_dst, (const unsigned long long*)c->offsets.p,
+                                    (const uint32_t*)c->sizes.p, (const uint32_t*)c->crcs.p, n_frag,
+                                    c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
     return SNAPPY_B200_OK;
@@ -310,6 +324,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->seqs.release(); c->nseq.release(); c->sizes.release(); c->offsets.release();
     c->d_in.release(); c->d_out.release();
+    c->crcs.release(); c->frame_ix.release(); c->frame_res.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -367,14 +382,14 @@ snappy_b200_status snappy_b200_compress_device(snappy_b200_ctx* c, const void* d
                                                void* d_dst, size_t dst_cap,
                                                unsigned long long* d_out_n, int mode) {
     if (!c || !d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
-    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, true);
+    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, 1);
 }
 
 snappy_b200_status snappy_b200_compress_fragments_device(snappy_b200_ctx* c, const void* d_src,
                                                          size_t n, void* d_dst, size_t dst_cap,
                                                          unsigned long long* d_out_n, int mode) {
     if (!c || !d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
-    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, false);
+    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, 0);
 }
 
 snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const void* d_src,
@@ -432,7 +447,7 @@ snappy_b200_status snappy_b200_compress(snappy_b200_ctx* c, const void* src, siz
     CU(c->d_out.reserve(cap + 64));
     if (n) CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
     CU(cudaEventRecord(c->ev0, c->stream));
-    snappy_b200_status st = compress_dev(c, c->d_in.p, n, c->d_out.p, cap, c->d_total, mode, true);
+    snappy_b200_status st = compress_dev(c, c->d_in.p, n, c->d_out.p, cap, c->d_total, mode, 1);
     if (st != SNAPPY_B200_OK) return st;
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
@@ -553,6 +568,140 @@ unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, c
     if (snappy_b200_uncompressed_length(source, (size_t)compressed_length, &ulen) != SNAPPY_B200_OK) return 1ul;
     return snappy_b200_uncompress(nullptr, source, (size_t)compressed_length, dest, ulen, &out_n) == SNAPPY_B200_OK
                ? 0ul : 1ul;
+}
+
+/* ---- Snappy framing format (tests/snappy/framing_format.txt) ---------------------------------- */
+
+size_t snappy_b200_frame_max_length(size_t n) {
+    const size_t chunks = (n + sb::kBlock - 1) / sb::kBlock;
+    return 10 + chunks * 40 + n + n / 6;                 /* id + per chunk: header, CRC, MaxCompressedLength slack */
+}
+
+snappy_b200_status snappy_b200_frame_compress_device(snappy_b200_ctx* c, const void* d_src, size_t n,
+                                                     void* d_dst, size_t dst_cap,
+                                                     unsigned long long* d_out_n, int mode) {
+    if (!c || !d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    return compress_dev(c, d_src, n, d_dst, dst_cap, d_out_n, mode, 2);
+}
+
+snappy_b200_status snappy_b200_frame_compress(snappy_b200_ctx* c, const void* src, size_t n, void* dst,
+                                              size_t dst_cap, size_t* out_n, int mode) {
+    if (!dst || !out_n || (!src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
+    const size_t cap = snappy_b200_frame_max_length(n);
+    if (dst_cap < cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < frame_max_length(n)");
+    if (!c) { snappy_b200_status st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(c->d_in.reserve(n + 64));
+    CU(c->d_out.reserve(cap + 64));
+    if (n) CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    snappy_b200_status st = compress_dev(c, c->d_in.p, n, c->d_out.p, cap, c->d_total, mode, 2);
+    if (st != SNAPPY_B200_OK) return st;
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const size_t total = (size_t)*c->h_total;
+    CU(cudaMemcpyAsync(dst, c->d_out.p, total, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    *out_n = total;
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_crc32c_chunks_device(snappy_b200_ctx* c, const void* d_src, size_t n,
+                                                    size_t chunk_len, uint32_t* d_masked) {
+    if (!c || !d_masked || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (chunk_len == 0 || chunk_len > sb::kBlock) return fail(SNAPPY_B200_INVALID_INPUT, "chunk_len must be 1..65536");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    const size_t chunks = (n + chunk_len - 1) / chunk_len;
+    if (chunks > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "too many chunks");
+    CU(sb::launch_crc32c_chunks((const uint8_t*)d_src, nullptr, nullptr, chunk_len, n, (uint32_t)chunk_len,
+                                (uint32_t)chunks, d_masked, c->stream, &c->launches));
+    return SNAPPY_B200_OK;
+}
+
+/* Header walk on the host (metadata only, like reading the varint preamble of a raw stream). */
+snappy_b200_status snappy_b200_frame_uncompressed_length(const void* src, size_t n, size_t* result) {
+    if (!src || !result) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    const uint8_t* s = (const uint8_t*)src;
+    static const uint8_t id[10] = {0xff, 0x06, 0x00, 0x00, 0x73, 0x4e, 0x61, 0x50, 0x70, 0x59};
+    if (n < 10 || memcmp(s, id, 10) != 0) return fail(SNAPPY_B200_INVALID_INPUT, "no stream identifier");
+    size_t pos = 0, out = 0;
+    while (pos < n) {
+        if (pos + 4 > n) return fail(SNAPPY_B200_INVALID_INPUT, "truncated chunk header");
+        const uint32_t type = s[pos], len = s[pos + 1] | (s[pos + 2] << 8) | ((uint32_t)s[pos + 3] << 16);
+        if (pos + 4 + len > n) return fail(SNAPPY_B200_INVALID_INPUT, "truncated chunk");
+        if (type == 0xff) {
+            if (len != 6 || memcmp(s + pos, id, 10) != 0) return fail(SNAPPY_B200_INVALID_INPUT, "bad stream identifier");
+        } else if (type == 0x00) {
+            if (len < 4) return fail(SNAPPY_B200_INVALID_INPUT, "short chunk");
+            size_t ulen = 0;
+            if (snappy_b200_uncompressed_length(s + pos + 8, len - 4, &ulen) != SNAPPY_B200_OK) return SNAPPY_B200_INVALID_INPUT;
+            if (ulen > sb::kBlock) return fail(SNAPPY_B200_INVALID_INPUT, "chunk larger than 65536 bytes");
+            out += ulen;
+        } else if (type == 0x01) {
+            if (len < 4 || len - 4 > sb::kBlock) return fail(SNAPPY_B200_INVALID_INPUT, "bad uncompressed chunk");
+            out += len - 4;
+        } else if (type >= 0x02 && type <= 0x7f) {
+            return fail(SNAPPY_B200_INVALID_INPUT, "reserved unskippable chunk");
+        }
+        pos += 4 + (size_t)len;
+    }
+    *result = out;
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_frame_uncompress_device(snappy_b200_ctx* c, const void* d_src, size_t n,
+                                                       void* d_dst, size_t dst_cap, size_t* out_n) {
+    if (!c || !d_src || !out_n || (!d_dst && dst_cap)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(c->frame_res.reserve(256));
+    sb::FrameWalkResult* d_res = (sb::FrameWalkResult*)c->frame_res.p;
+    uint32_t* d_bad = (uint32_t*)((uint8_t*)c->frame_res.p + 64);
+    sb::FrameWalkResult res;
+    size_t max_records = 2 * (dst_cap >> 16) + 1024;
+    for (int pass = 0;; ++pass) {
+        CU(c->frame_ix.reserve(max_records * sb::kFrameRecordBytes + 64));
+        CU(sb::launch_frame_walk((const uint8_t*)d_src, n, c->frame_ix.p, max_records, d_res, c->stream, &c->launches));
+        CU(cudaMemcpyAsync(&res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (res.error != 2 || pass) break;
+        max_records = (size_t)res.n_chunks;              /* the index was too small: now it is exact */
+    }
+    if (res.error) return fail(SNAPPY_B200_INVALID_INPUT, "malformed framed stream");
+    if (res.out_bytes > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < uncompressed length");
+    if (res.n_chunks > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "too many chunks");
+    CU(cudaMemsetAsync(d_bad, 0, sizeof(uint32_t), c->stream));
+    CU(sb::launch_frame_decode((const uint8_t*)d_src, (uint8_t*)d_dst, c->frame_ix.p, max_records,
+                               (uint32_t)res.n_chunks, d_bad, c->stream, &c->launches));
+    uint32_t bad = 0;
+    CU(cudaMemcpyAsync(&bad, d_bad, sizeof(bad), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (bad) return fail(SNAPPY_B200_INVALID_INPUT, "a chunk is malformed or fails its CRC-32C");
+    *out_n = (size_t)res.out_bytes;
+    return SNAPPY_B200_OK;
+}
+
+snappy_b200_status snappy_b200_frame_uncompress(snappy_b200_ctx* c, const void* src, size_t n, void* dst,
+                                                size_t dst_cap, size_t* out_n) {
+    if (!src || !out_n || (!dst && dst_cap)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    size_t ulen = 0;
+    snappy_b200_status st = snappy_b200_frame_uncompressed_length(src, n, &ulen);
+    if (st != SNAPPY_B200_OK) return st;
+    if (ulen > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < uncompressed length");
+    if (!c) { st = default_ctx(&c); if (st != SNAPPY_B200_OK) return st; }
+    if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    CU(c->d_in.reserve(n + 64));
+    CU(c->d_out.reserve(ulen + 64));
+    CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
+    size_t got = 0;
+    st = snappy_b200_frame_uncompress_device(c, c->d_in.p, n, c->d_out.p, ulen, &got);
+    if (st != SNAPPY_B200_OK) return st;
+    if (got) CU(cudaMemcpyAsync(dst, c->d_out.p, got, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *out_n = got;
+    return SNAPPY_B200_OK;
 }
 
 }  // extern "C"

@@ -30,6 +30,13 @@ struct DecodeParams {
     uint64_t out_cap;             // capacity per stream
     uint32_t* out_lens;           // decoded length of stream j, kDecodeError if malformed (may be nullptr)
     unsigned long long* out_len64;// single-stream flavour: length or ~0ull (may be nullptr)
+    // indexed flavour (framed streams, frame.cuh): when in_offs is set, stream j = in + in_offs[j]
+    // (in_sizes[j] bytes) decodes to out + out_offs[j] with capacity caps[j]; kinds[j] == 1 marks
+    // a stored (uncompressed) chunk that is copied as it is
+    const unsigned long long* in_offs = nullptr;
+    const unsigned long long* out_offs = nullptr;
+    const uint32_t* caps = nullptr;
+    const uint32_t* kinds = nullptr;
 };
 
 // n bytes d[0..n) = s[0..n), s read-only input (any alignment), all lanes of the warp
@@ -139,10 +146,17 @@ __global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (job >= p.n_jobs) return;
-    const uint8_t* __restrict__ src = p.in + (uint64_t)job * p.in_stride;
+    const uint8_t* __restrict__ src = p.in + (p.in_offs ? p.in_offs[job] : (uint64_t)job * p.in_stride);
     const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
-    uint8_t* dst = p.out + (uint64_t)job * p.out_stride;
-    const uint32_t got = decode_stream_global(src, n, dst, p.out_cap, lane);
+    uint8_t* dst = p.out + (p.out_offs ? p.out_offs[job] : (uint64_t)job * p.out_stride);
+    const uint64_t cap = p.caps ? (uint64_t)p.caps[job] : p.out_cap;
+    uint32_t got;
+    if (p.kinds && p.kinds[job] == 1) {                  // stored chunk
+        got = n <= cap ? n : kDecodeError;
+        if (got != kDecodeError) decode_literal(dst, src, n, lane);
+    } else {
+        got = decode_stream_global(src, n, dst, cap, lane);
+    }
     if (lane == 0) {
         if (p.out_lens) p.out_lens[job] = got;
         if (p.out_len64) *p.out_len64 = got == kDecodeError ? ~0ull : (unsigned long long)got;

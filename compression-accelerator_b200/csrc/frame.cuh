@@ -1,0 +1,241 @@
+// frame.cuh -- Snappy framing format (tests/snappy/framing_format.txt) on the device.
+//
+// A framed stream is the 10-byte stream identifier (framing_format.txt:68-75) followed by chunks
+// of at most 65,536 uncompressed bytes (:88-91), each: type byte, 3-byte LE length, masked
+// CRC-32C of the UNCOMPRESSED bytes (:38-57), then an ordinary Snappy stream of the chunk (:80-86)
+// -- exactly a fragment of the raw path with its own varint preamble, so the writer reuses the
+// parse / size / scan / emit kernels with per-job headers and only adds the CRC pass and the
+// chunk headers.  Chunks are independent: unlike a raw stream, a framed one decodes in parallel.
+//
+// CRC-32C (Castagnoli, reflected polynomial 0x82F63B78; RFC 3720 12.1, vectors B.4): one CTA per
+// chunk, 256 threads, each thread the raw remainder (init 0) of its 256-byte slice by 4-way table
+// slicing from shared memory; slices are combined in a tree with the linear operator "append 2^k
+// zero bytes" (32x32 bit matrices, precomputed by the host into constant memory).  The chunk is
+// laid out right-aligned in a virtual 64 KiB so every combine step shifts by a fixed amount; the
+// effect of the all-ones initial value, crc_update(0xFFFFFFFF, len zero bytes), is a product of
+// those operators over the bits of len.
+#pragma once
+#include "kernels.h"
+#include "snappy_device.cuh"
+#include "parse_pipe.cuh"   // GlobalSrc: unaligned, bounds-aware global loads
+
+namespace sb {
+
+constexpr uint32_t kCrcPoly = 0x82F63B78u;
+constexpr uint32_t kCrcMaskDelta = 0xa282ead8u;      // framing_format.txt:46-53
+constexpr uint32_t kFrameChunk = 65536;              // :88-91
+constexpr uint32_t kCrcThreads = 256;
+constexpr uint32_t kFrameIdLen = 10;
+
+struct CrcOps { uint32_t pow[17][32]; };             // pow[k][j] = image of bit j under "append 2^k zero bytes"
+__constant__ CrcOps g_crc_ops;
+
+__host__ __device__ inline uint32_t crc_mask(uint32_t x) { return ((x >> 15) | (x << 17)) + kCrcMaskDelta; }
+__host__ __device__ inline uint32_t crc_unmask(uint32_t m) { const uint32_t r = m - kCrcMaskDelta; return (r >> 17) | (r << 15); }
+
+inline void crc_ops_build(CrcOps& o) {               // host, once
+    for (int j = 0; j < 32; ++j) {
+        uint32_t v = 1u << j;
+        for (int b = 0; b < 8; ++b) v = (v >> 1) ^ ((v & 1u) ? kCrcPoly : 0u);
+        o.pow[0][j] = v;
+    }
+    for (int k = 1; k < 17; ++k)
+        for (int j = 0; j < 32; ++j) {
+            uint32_t v = o.pow[k - 1][j], r = 0;
+            for (int b = 0; b < 32; ++b) if ((v >> b) & 1u) r ^= o.pow[k - 1][b];
+            o.pow[k][j] = r;
+        }
+}
+
+__device__ __forceinline__ uint32_t crc_append_zeros(uint32_t v, int k) {   // 2^k zero bytes
+    uint32_t r = 0;
+#pragma unroll 8
+    for (int b = 0; b < 32; ++b) r ^= ((v >> b) & 1u) ? g_crc_ops.pow[k][b] : 0u;
+    return r;
+}
+
+struct CrcParams {
+    const uint8_t* base;                 // chunk c = base + (offs ? offs[c] : c*stride)
+    const unsigned long long* offs;
+    const uint32_t* lens;                // nullptr: min(fixed_len, n_total - c*stride)
+    uint64_t stride, n_total;
+    uint32_t fixed_len, n_chunks;
+    uint32_t* out_masked;                // masked CRC-32C of chunk c
+};
+
+__global__ void __launch_bounds__(kCrcThreads) crc32c_chunks_kernel(CrcParams p) {
+    __shared__ uint32_t T[4][256];
+    __shared__ uint32_t part[2][kCrcThreads];
+    const uint32_t t = threadIdx.x, c = blockIdx.x;
+    {
+        uint32_t v = t;
+        for (int b = 0; b < 8; ++b) v = (v >> 1) ^ ((v & 1u) ? kCrcPoly : 0u);
+        T[0][t] = v;
+    }
+    __syncthreads();
+    {
+        const uint32_t t0 = T[0][t];
+        const uint32_t t1 = (t0 >> 8) ^ T[0][t0 & 0xffu];
+        const uint32_t t2 = (t1 >> 8) ^ T[0][t1 & 0xffu];
+        T[1][t] = t1; T[2][t] = t2; T[3][t] = (t2 >> 8) ^ T[0][t2 & 0xffu];
+    }
+    __syncthreads();
+    const uint64_t off = p.offs ? p.offs[c] : (uint64_t)c * p.stride;
+    uint32_t len;
+    if (p.lens) len = p.lens[c];
+    else { const uint64_t left = p.n_total - off; len = left < p.fixed_len ? (uint32_t)left : p.fixed_len; }
+    if (len > kFrameChunk) len = kFrameChunk;            // callers never ask for more
+    GlobalSrc src{p.base + off};
+    // right-aligned: virtual position v holds data byte v - pad
+    const uint32_t pad = kFrameChunk - len;
+    uint32_t v0 = t * 256u, v1 = v0 + 256u, crc = 0;
+    if (v0 < pad) v0 = pad;
+    if (v0 < v1) {
+        uint32_t i = v0 - pad;
+        const uint32_t e = v1 - pad;
+        for (; ((e - i) & 3u) != 0; ++i)                 // leading bytes: the rest is whole words
+            crc = T[0][(crc ^ __ldg(p.base + off + i)) & 0xffu] ^ (crc >> 8);
+        for (; i + 16 <= e; i += 16) {
+            uint32_t w0, w1, w2, w3;
+            if (i + 20 <= len) src.ld16(i, w0, w1, w2, w3);
+            else { w0 = src.ld32_upto(i, len); w1 = src.ld32_upto(i + 4, len); w2 = src.ld32_upto(i + 8, len); w3 = src.ld32_upto(i + 12, len); }
+            crc ^= w0; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+            crc ^= w1; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+            crc ^= w2; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+            crc ^= w3; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+        }
+        for (; i < e; i += 4) {
+            crc ^= src.ld32_upto(i, len);
+            crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+        }
+    }
+    // tree: at level k neighbouring slices of 256 * 2^k bytes merge, left ++ right = shift(left) ^ right
+    part[0][t] = crc;
+    __syncthreads();
+    int cur = 0;
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t pairs = kCrcThreads >> (k + 1);
+        if (t < pairs) part[cur ^ 1][t] = crc_append_zeros(part[cur][2 * t], 8 + k) ^ part[cur][2 * t + 1];
+        __syncthreads();
+        cur ^= 1;
+    }
+    if (t == 0) {
+        uint32_t init = 0xffffffffu;                     // crc_update(~0, len zero bytes)
+        for (int k = 0; k < 17; ++k) if ((len >> k) & 1u) init = crc_append_zeros(init, k);
+        p.out_masked[c] = crc_mask(~(part[cur][0] ^ init));
+    }
+}
+
+// ---- writer ------------------------------------------------------------------------------------
+// sizes[j] (chunk's Snappy stream, varint included) -> bytes of the whole chunk (header + CRC + stream)
+__global__ void frame_bump_sizes_kernel(uint32_t* sizes, uint32_t n) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) sizes[j] += 8u;
+}
+
+// stream identifier + every chunk's 4-byte header and masked CRC (the Snappy stream follows at +8)
+__global__ void frame_headers_kernel(uint8_t* dst, const unsigned long long* offsets, const uint32_t* sizes,
+                                     const uint32_t* crcs, uint32_t n) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0) {
+        const uint8_t id[kFrameIdLen] = {0xff, 0x06, 0x00, 0x00, 0x73, 0x4e, 0x61, 0x50, 0x70, 0x59};
+        for (uint32_t i = 0; i < kFrameIdLen; ++i) dst[i] = id[i];
+    }
+    if (j >= n) return;
+    uint8_t* d = dst + offsets[j];
+    const uint32_t l = sizes[j] - 4u, crc = crcs[j];     // chunk length field: CRC + stream
+    d[0] = 0x00; d[1] = (uint8_t)l; d[2] = (uint8_t)(l >> 8); d[3] = (uint8_t)(l >> 16);
+    d[4] = (uint8_t)crc; d[5] = (uint8_t)(crc >> 8); d[6] = (uint8_t)(crc >> 16); d[7] = (uint8_t)(crc >> 24);
+}
+
+// ---- reader ------------------------------------------------------------------------------------
+struct FrameIndex {                      // one record per data chunk, filled by the walk
+    unsigned long long* in_off;          // payload (after header + CRC) in the framed stream
+    unsigned long long* out_off;         // where the chunk's bytes go
+    uint32_t* in_len;                    // payload bytes
+    uint32_t* ulen;                      // uncompressed bytes (from the payload's varint / the chunk length)
+    uint32_t* crc;                       // stored masked CRC
+    uint32_t* kind;                      // 0 compressed, 1 uncompressed
+};
+
+// index_base holds max_records records as parallel arrays (kFrameRecordBytes each, kernels.h):
+// in_off, out_off (u64), in_len, ulen, crc, kind, then the decode's got_len, got_crc (u32)
+struct FrameScratch { FrameIndex ix; uint32_t* got_len; uint32_t* got_crc; };
+__host__ __device__ inline FrameScratch frame_scratch(void* base, uint64_t m) {
+    FrameScratch f;
+    f.ix.in_off = (unsigned long long*)base;
+    f.ix.out_off = f.ix.in_off + m;
+    f.ix.in_len = (uint32_t*)(f.ix.out_off + m);
+    f.ix.ulen = f.ix.in_len + m;
+    f.ix.crc = f.ix.ulen + m;
+    f.ix.kind = f.ix.crc + m;
+    f.got_len = f.ix.kind + m;
+    f.got_crc = f.got_len + m;
+    return f;
+}
+
+// The chunk chain is a linked list through the stream: one thread follows it (16 K hops per GiB).
+__global__ void frame_walk_kernel(const uint8_t* __restrict__ src, uint64_t n, FrameIndex ix,
+                                  uint64_t max_records, FrameWalkResult* res) {
+    if (threadIdx.x || blockIdx.x) return;
+    uint64_t pos = 0, out = 0, cnt = 0;
+    uint32_t err = 0;
+    bool first = true;
+    while (pos < n) {
+        if (pos + 4 > n) { err = 1; break; }
+        const uint32_t type = src[pos];
+        const uint32_t len = src[pos + 1] | ((uint32_t)src[pos + 2] << 8) | ((uint32_t)src[pos + 3] << 16);
+        if (pos + 4 + len > n) { err = 1; break; }
+        if (first && type != 0xff) { err = 1; break; }                       // :20-21
+        first = false;
+        if (type == 0xff) {                                                  // :68-78
+            const uint8_t id[6] = {0x73, 0x4e, 0x61, 0x50, 0x70, 0x59};
+            bool ok = len == 6;
+            for (uint32_t i = 0; ok && i < 6; ++i) ok = src[pos + 4 + i] == id[i];
+            if (!ok) { err = 1; break; }
+        } else if (type == 0x00 || type == 0x01) {
+            if (len < 4) { err = 1; break; }
+            const uint64_t pay = pos + 8;
+            const uint32_t plen = len - 4;
+            const uint32_t crc = src[pos + 4] | ((uint32_t)src[pos + 5] << 8) | ((uint32_t)src[pos + 6] << 16) |
+                                 ((uint32_t)src[pos + 7] << 24);
+            uint32_t ulen = plen;
+            if (type == 0x00) {                                              // varint32 preamble of the chunk's stream
+                ulen = 0;
+                uint32_t shift = 0, i = 0;
+                for (;; ++i) {
+                    if (i >= plen || shift > 28) { err = 1; break; }
+                    const uint32_t b = src[pay + i];
+                    if (shift == 28 && (b & 0x7fu) > 15u) { err = 1; break; }
+                    ulen |= (b & 0x7fu) << shift;
+                    if (b < 128) break;
+                    shift += 7;
+                }
+                if (err) break;
+            }
+            if (ulen > kFrameChunk) { err = 1; break; }                      // :88-91, :104-106
+            if (cnt < max_records) {
+                ix.in_off[cnt] = pay; ix.out_off[cnt] = out; ix.in_len[cnt] = plen;
+                ix.ulen[cnt] = ulen; ix.crc[cnt] = crc; ix.kind[cnt] = type;
+            } else if (!err) err = 2;
+            ++cnt;
+            out += ulen;
+        } else if (type >= 0x02 && type <= 0x7f) {                           // :122-128 unskippable
+            err = 1; break;
+        }                                                                    // 0x80..0xfe: skip (:111-120, :131-138)
+        pos += 4 + (uint64_t)len;
+    }
+    if (first && n) err = 1;
+    if (n == 0) err = 1;                                                     // no stream identifier
+    res->n_chunks = cnt; res->out_bytes = out; res->error = err; res->pad = 0;
+}
+
+// stored vs recomputed CRC and decode status of every chunk -> one flag
+__global__ void frame_verify_kernel(FrameIndex ix, const uint32_t* got_len, const uint32_t* got_crc,
+                                    uint32_t n, uint32_t* bad) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    if (got_len[j] != ix.ulen[j] || got_crc[j] != ix.crc[j]) atomicOr(bad, 1u);
+}
+
+}  // namespace sb

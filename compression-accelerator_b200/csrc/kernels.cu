@@ -17,6 +17,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "parse_fast.cuh"
 #include "emit.cuh"
 #include "decode.cuh"
+#include "frame.cuh"
 #include <type_traits>
 
 namespace sb {
@@ -365,8 +366,12 @@ cudaError_t kernels_init() {
     e = cudaFuncSetAttribute(parse_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)fast_layout(kBlock).total);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(decode_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(kStageWarps * (3 * kStageOutMax + 128)));
+    e = cudaFuncSetAttribute(decode_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(kStageWarps * (3 * kStageOutMax + 128)));
+    if (e != cudaSuccess) return e;
+    static CrcOps ops;                                      // "append 2^k zero bytes" operators of CRC-32C
+    crc_ops_build(ops);
+    return cudaMemcpyToSymbol(g_crc_ops, &ops, sizeof(ops));
 }
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
@@ -419,6 +424,60 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
     } else {
         decode_kernel<<<(count + 3) / 4, 128, 0, st>>>(p);
     }
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- framing ------------------------------------------------------------------------------------
+cudaError_t launch_crc32c_chunks(const uint8_t* base, const unsigned long long* offs, const uint32_t* lens,
+                                 uint64_t stride, uint64_t n_total, uint32_t fixed_len, uint32_t n_chunks,
+                                 uint32_t* out_masked, cudaStream_t st, unsigned long long* launches) {
+    if (n_chunks == 0) return cudaSuccess;
+    CrcParams p;
+    p.base = base; p.offs = offs; p.lens = lens; p.stride = stride; p.n_total = n_total;
+    p.fixed_len = fixed_len; p.n_chunks = n_chunks; p.out_masked = out_masked;
+    crc32c_chunks_kernel<<<n_chunks, kCrcThreads, 0, st>>>(p);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_bump(uint32_t* sizes, uint32_t n, cudaStream_t st, unsigned long long* launches) {
+    if (n == 0) return cudaSuccess;
+    frame_bump_sizes_kernel<<<(n + 255) / 256, 256, 0, st>>>(sizes, n);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_headers(uint8_t* dst, const unsigned long long* offsets, const uint32_t* sizes,
+                                 const uint32_t* crcs, uint32_t n, cudaStream_t st, unsigned long long* launches) {
+    frame_headers_kernel<<<(n + 256) / 256, 256, 0, st>>>(dst, offsets, sizes, crcs, n);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, uint64_t max_records,
+                              FrameWalkResult* d_result, cudaStream_t st, unsigned long long* launches) {
+    frame_walk_kernel<<<1, 32, 0, st>>>(src, n, frame_scratch(index_base, max_records).ix, max_records, d_result);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_decode(const uint8_t* src, uint8_t* dst, void* index_base, uint64_t max_records,
+                                uint32_t n_chunks, uint32_t* d_bad, cudaStream_t st,
+                                unsigned long long* launches) {
+    if (n_chunks == 0) return cudaSuccess;
+    const FrameScratch f = frame_scratch(index_base, max_records);
+    DecodeParams p;
+    p.in = src; p.in_stride = 0; p.in_sizes = f.ix.in_len; p.in_size = 0; p.n_jobs = n_chunks;
+    p.out = dst; p.out_stride = 0; p.out_cap = 0; p.out_lens = f.got_len; p.out_len64 = nullptr;
+    p.in_offs = f.ix.in_off; p.out_offs = f.ix.out_off; p.caps = f.ix.ulen; p.kinds = f.ix.kind;
+    decode_kernel<<<(n_chunks + 3) / 4, 128, 0, st>>>(p);
+    if (launches) ++*launches;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    e = launch_crc32c_chunks(dst, f.ix.out_off, f.ix.ulen, 0, 0, 0, n_chunks, f.got_crc, st, launches);
+    if (e != cudaSuccess) return e;
+    frame_verify_kernel<<<(n_chunks + 255) / 256, 256, 0, st>>>(f.ix, f.got_len, f.got_crc, n_chunks, d_bad);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -72,6 +72,29 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
                           uint32_t* out_lens, unsigned long long* out_len64, cudaStream_t st,
                           unsigned long long* launches);
 
+// ---- Snappy framing format (frame.cuh; tests/snappy/framing_format.txt) -------------------------
+// Masked CRC-32C of `n_chunks` chunks of at most 65,536 bytes: chunk c = base + (offs ? offs[c] :
+// c*stride), lens[c] bytes (lens == nullptr: min(fixed_len, n_total - c*stride)).
+cudaError_t launch_crc32c_chunks(const uint8_t* base, const unsigned long long* offs, const uint32_t* lens,
+                                 uint64_t stride, uint64_t n_total, uint32_t fixed_len, uint32_t n_chunks,
+                                 uint32_t* out_masked, cudaStream_t st, unsigned long long* launches);
+// writer: sizes[j] += 8 (chunk header + CRC); then, after the scan, identifier + chunk headers
+cudaError_t launch_frame_bump(uint32_t* sizes, uint32_t n, cudaStream_t st, unsigned long long* launches);
+cudaError_t launch_frame_headers(uint8_t* dst, const unsigned long long* offsets, const uint32_t* sizes,
+                                 const uint32_t* crcs, uint32_t n, cudaStream_t st, unsigned long long* launches);
+// reader: chunk index (kFrameRecordBytes per record at index_base), decode + CRC check of all chunks
+constexpr size_t kFrameRecordBytes = 40;
+struct FrameWalkResult {
+    unsigned long long n_chunks, out_bytes;
+    uint32_t error;                      // 0 ok, 1 malformed, 2 index too small (n_chunks is still exact)
+    uint32_t pad;
+};
+cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, uint64_t max_records,
+                              FrameWalkResult* d_result, cudaStream_t st, unsigned long long* launches);
+cudaError_t launch_frame_decode(const uint8_t* src, uint8_t* dst, void* index_base, uint64_t max_records,
+                                uint32_t n_chunks, uint32_t* d_bad, cudaStream_t st,
+                                unsigned long long* launches);
+
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 
 }  // namespace sb

@@ -106,6 +106,35 @@ snappy_b200_status snappy_b200_uncompress_batch_device(snappy_b200_ctx* ctx, con
                                                        size_t count, void* d_dst, size_t out_stride,
                                                        uint32_t* d_out_lens);
 
+/* ---- Snappy framing format ------------------------------------------------------------------------
+ * tests/snappy/framing_format.txt: stream identifier (:68-75), then chunks of at most 65,536
+ * uncompressed bytes (:88-91): type, 3-byte length, masked CRC-32C of the uncompressed bytes (:38-57),
+ * an ordinary Snappy stream of the chunk (:80-86).  The reference vendors the specification only (no
+ * writer or reader), so these entries have no reference function to mirror; they are SURVEY.md 8(f)
+ * rank 2.  Chunks are independent, so -- unlike a raw stream -- a framed stream of any size decodes
+ * in parallel, and every chunk is checked against its CRC.  The writer emits compressed chunks
+ * (type 0x00) of 65,536 bytes (the last one shorter); the reader also accepts uncompressed (0x01),
+ * padding / skippable (0x80-0xfe) and repeated identifier chunks, and rejects 0x02-0x7f (:122-128). */
+size_t snappy_b200_frame_max_length(size_t n);
+/* host pointers, synchronous */
+snappy_b200_status snappy_b200_frame_compress(snappy_b200_ctx* ctx, const void* src, size_t n, void* dst,
+                                              size_t dst_cap, size_t* out_n, int mode);
+snappy_b200_status snappy_b200_frame_uncompress(snappy_b200_ctx* ctx, const void* src, size_t n, void* dst,
+                                                size_t dst_cap, size_t* out_n);
+/* total uncompressed bytes of a framed stream in host memory (header walk only) */
+snappy_b200_status snappy_b200_frame_uncompressed_length(const void* src, size_t n, size_t* result);
+/* device pointers.  compress: asynchronous on the context's stream, *d_out_n (device) = stream length.
+ * uncompress: synchronous (the status depends on every chunk's CRC), *out_n is a host word. */
+snappy_b200_status snappy_b200_frame_compress_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
+                                                     void* d_dst, size_t dst_cap,
+                                                     unsigned long long* d_out_n, int mode);
+snappy_b200_status snappy_b200_frame_uncompress_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
+                                                       void* d_dst, size_t dst_cap, size_t* out_n);
+/* masked CRC-32C (framing_format.txt:38-57; RFC 3720 12.1) of consecutive chunk_len-byte chunks
+ * (chunk_len <= 65536, last one shorter) of a device buffer; d_masked[i] for chunk i; asynchronous. */
+snappy_b200_status snappy_b200_crc32c_chunks_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
+                                                    size_t chunk_len, uint32_t* d_masked);
+
 /* Write varint32(n) at dst (host memory), return its length 1..5
  * (tests/snappy/snappy-stubs-internal.h:552-578). */
 size_t snappy_b200_varint32(void* dst, uint32_t n);

@@ -309,3 +309,21 @@ size_t port_fast_compress(const uint8_t *in, size_t n, uint8_t *out) {
     }
     return op;
 }
+
+/* ---- CRC-32C for the framing format (tests/snappy/framing_format.txt:38-57) -------------------------
+ * RFC 3720 12.1: polynomial 0x1EDC6F41, reflected 0x82F63B78, initial value and final xor all ones.
+ * Bit-at-a-time restatement (the checker need not be fast); pinned by the RFC's B.4 vectors in
+ * tests/test_framing.py. */
+uint32_t port_crc32c(const uint8_t *p, size_t n) {
+    uint32_t crc = 0xffffffffu;
+    for (size_t i = 0; i < n; ++i) {
+        crc ^= p[i];
+        for (int b = 0; b < 8; ++b) crc = (crc >> 1) ^ ((crc & 1u) ? 0x82F63B78u : 0u);
+    }
+    return ~crc;
+}
+
+uint32_t port_crc32c_masked(const uint8_t *p, size_t n) {       /* framing_format.txt:46-53 */
+    const uint32_t x = port_crc32c(p, n);
+    return ((x >> 15) | (x << 17)) + 0xa282ead8u;
+}

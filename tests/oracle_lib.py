@@ -74,6 +74,17 @@ class Port(_Lib):
         self.lib.port_fast_compress.restype = C.c_size_t
         self.lib.port_fast_compress.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p]
 
+    def crc32c(self, data: bytes) -> int:
+        """CRC-32C (RFC 3720 12.1), oracle/snappy_port.c port_crc32c."""
+        self.lib.port_crc32c.restype = C.c_uint32
+        self.lib.port_crc32c.argtypes = [C.c_char_p, C.c_size_t]
+        return self.lib.port_crc32c(data, len(data))
+
+    def crc32c_masked(self, data: bytes) -> int:
+        self.lib.port_crc32c_masked.restype = C.c_uint32
+        self.lib.port_crc32c_masked.argtypes = [C.c_char_p, C.c_size_t]
+        return self.lib.port_crc32c_masked(data, len(data))
+
     def fast_compress(self, data: bytes) -> bytes:
         """Sequential model of libsnappy_b200's FAST mode (oracle/snappy_port.c, port_fast_compress):
         defines that mode's stream; not a restatement of the reference."""
@@ -143,3 +154,55 @@ def ref() -> Ref:
 def checker():
     """The strongest checker available: the compiled reference if present, else the port."""
     return ref() if have_ref() else port()
+
+
+# ---- Snappy framing format (tests/snappy/framing_format.txt), CPU restatement ------------------
+STREAM_ID = bytes([0xff, 0x06, 0x00, 0x00, 0x73, 0x4e, 0x61, 0x50, 0x70, 0x59])   # :68-75
+FRAME_CHUNK = 65536                                                               # :88-91
+
+
+def frame_compress(data: bytes, compress=None) -> bytes:
+    """Writer with the library's policy: identifier, then one compressed chunk (type 0x00) per 65,536
+    input bytes: 3-byte LE length of (CRC + stream), masked CRC-32C of the uncompressed bytes
+    (:38-57, :80-86), the chunk's own Snappy stream."""
+    compress = compress or checker().compress
+    out = bytearray(STREAM_ID)
+    for i in range(0, len(data), FRAME_CHUNK):
+        chunk = data[i:i + FRAME_CHUNK]
+        body = compress(chunk)
+        ln = 4 + len(body)
+        out += bytes([0x00, ln & 0xff, (ln >> 8) & 0xff, (ln >> 16) & 0xff])
+        out += port().crc32c_masked(chunk).to_bytes(4, "little")
+        out += body
+    return bytes(out)
+
+
+def frame_uncompress(data: bytes) -> bytes:
+    """Reader: every chunk type of the specification; raises ValueError on malformed input."""
+    if data[:10] != STREAM_ID:
+        raise ValueError("no stream identifier")
+    out = bytearray()
+    pos = 0
+    while pos < len(data):
+        if pos + 4 > len(data):
+            raise ValueError("truncated header")
+        typ = data[pos]
+        ln = int.from_bytes(data[pos + 1:pos + 4], "little")
+        body = data[pos + 4:pos + 4 + ln]
+        if len(body) != ln:
+            raise ValueError("truncated chunk")
+        if typ == 0xff:
+            if data[pos:pos + 10] != STREAM_ID:
+                raise ValueError("bad identifier")
+        elif typ in (0x00, 0x01):
+            if ln < 4:
+                raise ValueError("short chunk")
+            crc = int.from_bytes(body[:4], "little")
+            raw = port().uncompress(bytes(body[4:]), FRAME_CHUNK) if typ == 0x00 else bytes(body[4:])
+            if len(raw) > FRAME_CHUNK or port().crc32c_masked(raw) != crc:
+                raise ValueError("bad chunk")
+            out += raw
+        elif 0x02 <= typ <= 0x7f:
+            raise ValueError("reserved unskippable chunk")
+        pos += 4 + ln
+    return bytes(out)

@@ -1,0 +1,161 @@
+"""Snappy framing format (tests/snappy/framing_format.txt): CRC-32C, the framed
+writer and the parallel, CRC-checked reader.  The reference vendors only the specification, so the
+checker is a CPU restatement (tests/oracle_lib.py frame_compress / frame_uncompress, CRC-32C in
+oracle/snappy_port.c) pinned by the RFC 3720 B.4 vectors the specification points at (:43-44)."""
+import numpy as np
+import pytest
+
+import corpus
+import oracle_lib
+
+# RFC 3720 B.4 "CRC Examples": 32 bytes of zeroes, of ones, incrementing, decrementing
+RFC_VECTORS = [
+    (bytes(32), 0x8A9136AA),
+    (bytes([0xff] * 32), 0x62A8AB43),
+    (bytes(range(32)), 0x46DD794E),
+    (bytes(range(31, -1, -1)), 0x113FDB5C),
+]
+
+
+def _unmask(m):
+    r = (m - 0xa282ead8) & 0xffffffff
+    return ((r >> 17) | (r << 15)) & 0xffffffff
+
+
+def test_crc32c_oracle_rfc3720_vectors():
+    p = oracle_lib.port()
+    for data, want in RFC_VECTORS:
+        assert p.crc32c(data) == want
+        assert _unmask(p.crc32c_masked(data)) == want
+    assert p.crc32c(b"") == 0
+    assert p.crc32c(b"123456789") == 0xE3069283                      # the usual check value
+
+
+def test_framing_restatement_round_trip():
+    data = corpus.fixture("alice29.txt")
+    framed = oracle_lib.frame_compress(data)
+    assert framed[:10] == oracle_lib.STREAM_ID
+    assert framed[10] == 0x00                                         # first chunk: compressed data
+    assert oracle_lib.frame_uncompress(framed) == data
+    # chunk structure: 3 chunks (152,089 bytes), lengths add up to the stream
+    pos, chunks = 10, 0
+    while pos < len(framed):
+        pos += 4 + int.from_bytes(framed[pos + 1:pos + 4], "little")
+        chunks += 1
+    assert pos == len(framed) and chunks == 3
+    bad = bytearray(framed); bad[30] ^= 1
+    with pytest.raises(ValueError):
+        oracle_lib.frame_uncompress(bytes(bad))
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+def test_crc32c_device_vectors(ctx):
+    import torch
+    for data, want in RFC_VECTORS + [(b"123456789", 0xE3069283), (b"a", oracle_lib.port().crc32c(b"a"))]:
+        t = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+        got = ctx.crc32c_chunks_device(t)
+        ctx.sync()
+        assert _unmask(int(got[0].item()) & 0xffffffff) == want, data[:8]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,chunk", [(65536, 65536), (200000, 65536), (70001, 4096), (1 << 20, 65536),
+                                     (12345, 1000), (5, 3), (65536 * 3 + 1, 65535)])
+def test_crc32c_device_chunks_equal_oracle(ctx, n, chunk):
+    import torch
+    data = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n + 3)[3:]          # unaligned source
+    t = torch.from_numpy(np.ascontiguousarray(corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n + 3))).cuda()[3:]
+    got = ctx.crc32c_chunks_device(t, chunk)
+    ctx.sync()
+    got = got.cpu().numpy().astype(np.uint32)
+    p = oracle_lib.port()
+    raw = data.tobytes()
+    want = [p.crc32c_masked(raw[i:i + chunk]) for i in range(0, n, chunk)]
+    assert got.tolist() == want
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["alice29.txt", "html", "fireworks.jpeg", "all-mtg-cards.txt"])
+def test_frame_compress_equals_restatement(ctx, oracle, name):
+    data = corpus.fixture(name)
+    got = ctx.frame_compress(data)
+    assert got == oracle_lib.frame_compress(data, oracle.compress)
+    assert ctx.frame_uncompress(got) == data
+    assert oracle_lib.frame_uncompress(got) == data
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [0, 1, 14, 65535, 65536, 65537, 131072, 200001])
+def test_frame_edge_sizes(ctx, oracle, n):
+    data = corpus.random_ascii(n).tobytes() if n % 2 else (b"ab" * (n // 2))
+    got = ctx.frame_compress(data)
+    assert got == oracle_lib.frame_compress(data, oracle.compress)
+    assert ctx.frame_uncompress(got) == data
+
+
+@pytest.mark.gpu
+def test_frame_fast_mode_round_trips(ctx):
+    data = corpus.fixture("all-mtg-cards.txt")
+    got = ctx.frame_compress(data, mode="fast")
+    assert oracle_lib.frame_uncompress(got) == data
+    assert ctx.frame_uncompress(got) == data
+
+
+@pytest.mark.gpu
+def test_frame_reader_accepts_every_chunk_type(ctx):
+    """Uncompressed chunks (:94-106), padding (:109-118), skippable (:131-138), repeated identifier (:76-78)."""
+    p = oracle_lib.port()
+    a, b = b"hello framing " * 100, corpus.fixture("html")[:5000]
+
+    def chunk(typ, body):
+        return bytes([typ]) + len(body).to_bytes(3, "little") + body
+
+    s = oracle_lib.STREAM_ID
+    s += chunk(0x01, p.crc32c_masked(a).to_bytes(4, "little") + a)
+    s += chunk(0xfe, bytes(37))
+    s += chunk(0x80, b"skip me")
+    s += oracle_lib.STREAM_ID
+    s += chunk(0x00, p.crc32c_masked(b).to_bytes(4, "little") + p.compress(b))
+    s += chunk(0xfd, b"")
+    assert ctx.frame_uncompress(s) == a + b
+    assert oracle_lib.frame_uncompress(s) == a + b
+
+
+@pytest.mark.gpu
+def test_frame_reader_rejects_bad_streams(ctx, pkg):
+    p = oracle_lib.port()
+    data = corpus.fixture("alice29.txt")
+    good = ctx.frame_compress(data)
+    cases = {}
+    x = bytearray(good); x[14] ^= 0x40; cases["crc"] = bytes(x)                  # stored CRC flipped
+    x = bytearray(good); x[40] ^= 0x01; cases["payload"] = bytes(x)              # payload bit flipped
+    cases["no id"] = good[10:]
+    cases["truncated"] = good[:-5]
+    cases["reserved"] = good + bytes([0x02, 0, 0, 0])
+    cases["bad id"] = good + bytes([0xff, 6, 0, 0]) + b"sNaPpX"
+    big = b"z" * 70000
+    cases["chunk too large"] = oracle_lib.STREAM_ID + bytes([0x01]) + (len(big) + 4).to_bytes(3, "little") + \
+        p.crc32c_masked(big).to_bytes(4, "little") + big
+    for name, s in cases.items():
+        with pytest.raises(pkg.SnappyB200Error):
+            ctx.frame_uncompress(s)
+
+
+@pytest.mark.gpu
+def test_frame_device_entries_large(ctx):
+    """64 MiB through the device entries: chunk count, CRCs, parallel decode, byte equality."""
+    import torch
+    n = 64 << 20
+    host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)
+    src = torch.from_numpy(host).cuda()
+    dst, out_n = ctx.frame_compress_device(src)
+    ctx.sync()
+    total = int(out_n.item())
+    back = torch.empty(n, dtype=torch.uint8, device="cuda")
+    got = ctx.frame_uncompress_device(dst, total, back)
+    assert got == n and torch.equal(back, src)
+    # the first chunk is what the restatement writes
+    first_len = 4 + int.from_bytes(bytes(dst[11:14].cpu().numpy()), "little")
+    want = oracle_lib.frame_compress(host[:65536].tobytes())
+    assert bytes(dst[:10 + first_len].cpu().numpy()) == want
