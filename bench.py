@@ -150,6 +150,47 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def next_rows(ctx, src, stream, torch, peak):
+    """SURVEY.md 8(f) rows measured on the same text, device-resident, CUDA events on the library's
+    stream: the decompressor on 4 KiB pages, the CRC-32C pass, the framed writer and the framed
+    (parallel, CRC-checked) reader.  Reported beside the headline; not part of `value`."""
+    n = src.numel()
+
+    def ev_ms(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    out = {}
+    page, count = 4096, n // 4096
+    comp, ostride, sizes = ctx.compress_batch_device(src, page, page, count)
+    back, lens = ctx.uncompress_batch_device(comp, ostride, sizes, count, page)
+    ms = ev_ms(lambda: ctx.uncompress_batch_device(comp, ostride, sizes, count, page, dst=back, out_lens=lens))
+    comp_bytes = int(sizes.sum().item())
+    out["uncompress_4k_pages"] = {"value": n / ms / 1e6, "unit": "GB/s decoded", "ms": ms,
+                                  "roofline_frac": (n + comp_bytes) / ms / 1e6 / peak,
+                                  "identical": bool(torch.equal(back[:n], src))}
+    del comp, back
+    crcs = ctx.crc32c_chunks_device(src)
+    ms = ev_ms(lambda: ctx.crc32c_chunks_device(src, out=crcs))
+    out["crc32c_64k_chunks"] = {"value": n / ms / 1e6, "unit": "GB/s", "ms": ms, "roofline_frac": n / ms / 1e6 / peak}
+    fdst, fout = ctx.frame_compress_device(src)
+    ms = ev_ms(lambda: ctx.frame_compress_device(src, dst=fdst, out_n=fout))
+    total = int(fout.item())
+    out["frame_compress"] = {"value": n / ms / 1e6, "unit": "GB/s in", "ms": ms, "framed_bytes": total}
+    back = torch.empty(n, dtype=torch.uint8, device=src.device)
+    ms = ev_ms(lambda: ctx.frame_uncompress_device(fdst, total, back))
+    out["frame_uncompress"] = {"value": n / ms / 1e6, "unit": "GB/s decoded", "ms": ms,
+                               "identical": bool(torch.equal(back, src))}
+    return out
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -270,6 +311,12 @@ def run_ours(args):
         dist.all_reduce(e2e_o, op=dist.ReduceOp.MAX)
     mode_now[0] = args.mode
 
+    extra = None
+    if rank == 0 and world == 1:
+        try:
+            extra = next_rows(ctx, src, stream, torch, measured_peak()[0])
+        except Exception as e:                     # never lose the headline line to a side measurement
+            extra = {"error": repr(e)}
     if rank == 0:
         peak, peak_src = measured_peak()
         pms = sorted(parse_ms)[len(parse_ms) // 2]
@@ -307,6 +354,7 @@ def run_ours(args):
                            "parse_kernel_ms": sorted(o_parse)[1],
                            "roofline_frac": (n + comp_o) / (sorted(o_parse)[1] * 1e-3) / 1e9 / peak,
                            "traffic": measured_traffic(other)},
+            "next_rows": extra,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
