@@ -48,6 +48,16 @@ struct DevBuf {
 
 }  // namespace
 
+// Parse streams of the chunked host entry.  A stream starts its next chunk only when ALL fragments of
+// its current one are done, so with S streams about S-1 chunks' worth of fragments are in flight: it
+// takes 8 x 16 MiB (2048 fragments) to keep the 888 resident slots of the exact parser full.
+constexpr int kParseStreams = 8;
+inline int pipe_streams() {
+    static const int n = [] { const char* e = getenv("SNAPPY_B200_PARSE_STREAMS"); int v = e ? atoi(e) : kParseStreams;
+                              return v < 1 ? 1 : v > kParseStreams ? kParseStreams : v; }();
+    return n;
+}
+
 struct snappy_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -62,7 +72,9 @@ struct snappy_b200_ctx {
     float last_ms = 0.f;
     // chunk pipeline of the host entry: H2D stream, parse streams, D2H stream; per-chunk events;
     // running stream length mirrored into mapped pinned host words by the scan kernel
-    cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_parse[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_parse[kParseStreams] = {};
+    cudaStream_t s_emit = nullptr;             // high priority: size/scan/emit of the exact mode's chunks
+    cudaEvent_t ev_done = nullptr;
     cudaEvent_t ev_start = nullptr;
     std::vector<cudaEvent_t> ev_h, ev_p, ev_e;
     unsigned long long* h_run = nullptr;       // pinned + mapped, kMaxChunks words
@@ -158,7 +170,7 @@ constexpr size_t kPipeMinBytes = 24u << 20;     // below this one H2D + one D2H 
 // little more than one resident wave of the pipelined parser), smaller ones an eighth.
 size_t pipe_chunk_bytes(size_t n, bool fast) {
     static const size_t env = [] { const char* e = getenv("SNAPPY_B200_CHUNK_MIB"); return e ? (size_t)atol(e) << 20 : (size_t)0; }();
-    // measured on 1 GiB text: exact 16 MiB 27.8 GB/s vs 64 MiB 26.8; fast 32 MiB 50.0 vs 64 MiB 48.5
+    // measured on 1 GiB text (8 parse streams): exact 16 MiB 36.0 ms, 32 MiB 36.4, 8 MiB 44; fast 32 MiB 21.2 ms, 16 MiB 22.6
     size_t c = env ? env : (n >= (256u << 20) ? (fast ? (32u << 20) : (16u << 20)) : n / 8);
     c = (c + sb::kBlock - 1) / sb::kBlock * sb::kBlock;
     if (c < (4u << 20)) c = 4u << 20;
@@ -171,6 +183,10 @@ snappy_b200_status ensure_pipe(snappy_b200_ctx* c, size_t n_chunks) {
         CU(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
         for (auto& s : c->s_parse) CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        int least = 0, greatest = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        CU(cudaStreamCreateWithPriority(&c->s_emit, cudaStreamNonBlocking, greatest));
+        CU(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_start, cudaEventDisableTiming));
         CU(cudaHostAlloc((void**)&c->h_run, kMaxChunks * sizeof(unsigned long long), cudaHostAllocMapped));
         CU(cudaHostGetDevicePointer((void**)&c->h_run_dev, c->h_run, 0));
@@ -211,6 +227,13 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     CU(cudaEventRecord(c->ev_start, c->stream));
     CU(cudaStreamWaitEvent(c->s_h2d, c->ev_start, 0));
     CU(cudaEventRecord(c->ev0, c->stream));
+    // size/scan/emit stream.  Exact mode: a high-priority stream, so these short kernels take free SM
+    // slots ahead of the queued parse CTAs and a chunk's bytes reach the D2H copy early (measured
+    // 38.7 -> 36.0 ms per GiB).  Fast mode is PCIe-bound and its emit pass is heavier: priority only
+    // delays the parse there (21.2 -> 22.7 ms), so it stays on the context's stream.
+    static const bool prio_on = [] { const char* e = getenv("SNAPPY_B200_STREAM_PRIO"); return !e || atoi(e) != 0; }();
+    cudaStream_t es = (mode == SNAPPY_B200_FAST || !prio_on) ? c->stream : c->s_emit;
+    if (es != c->stream) CU(cudaStreamWaitEvent(es, c->ev_start, 0));
     for (size_t k = 0; k < n_chunks; ++k) {
         const size_t lo = k * chunk, len = (n - lo < chunk) ? n - lo : chunk;
         const uint32_t f0 = (uint32_t)(lo / sb::kBlock);
@@ -230,17 +253,21 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         p.out = d_out;
         p.out_stride = 0;
         p.offsets = (const unsigned long long*)c->offsets.p + f0;
-        cudaStream_t ps = c->s_parse[k & 3];
+        cudaStream_t ps = c->s_parse[k % pipe_streams()];
         CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
         CU(sb::launch_parse(p, mode, ps, &c->launches));
         CU(cudaEventRecord(c->ev_p[k], ps));
-        CU(cudaStreamWaitEvent(c->stream, c->ev_p[k], 0));
-        CU(sb::launch_size(p, c->stream, &c->launches));
+        CU(cudaStreamWaitEvent(es, c->ev_p[k], 0));
+        CU(sb::launch_size(p, es, &c->launches));
         CU(sb::launch_scan(p.sizes, p.n_jobs, (unsigned long long*)c->offsets.p + f0, k == 0 ? hdr : 0,
-                           (uint32_t)n, d_out, c->d_total, c->stream, &c->launches,
+                           (uint32_t)n, d_out, c->d_total, es, &c->launches,
                            k == 0 ? nullptr : c->d_total, c->h_run_dev + k));
-        CU(sb::launch_emit(p, c->stream, &c->launches));
-        CU(cudaEventRecord(c->ev_e[k], c->stream));
+        CU(sb::launch_emit(p, es, &c->launches));
+        CU(cudaEventRecord(c->ev_e[k], es));
+    }
+    if (es != c->stream) {                                   // the context's stream stays the call's timeline
+        CU(cudaEventRecord(c->ev_done, es));
+        CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));
     }
     CU(cudaEventRecord(c->ev1, c->stream));
     // drain: as soon as chunk k's elements are in place its byte range goes back to the host
@@ -336,6 +363,8 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
     for (auto s_ : c->s_parse) if (s_) cudaStreamDestroy(s_);
+    if (c->s_emit) cudaStreamDestroy(c->s_emit);
+    if (c->ev_done) cudaEventDestroy(c->ev_done);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     for (auto e_ : c->ev_h) cudaEventDestroy(e_);
     for (auto e_ : c->ev_p) cudaEventDestroy(e_);
