@@ -8,8 +8,9 @@
 // chunk headers.  Chunks are independent: unlike a raw stream, a framed one decodes in parallel.
 //
 // CRC-32C (Castagnoli, reflected polynomial 0x82F63B78; RFC 3720 12.1, vectors B.4): one CTA per
-// chunk, 256 threads, each thread the raw remainder (init 0) of its 256-byte slice by 4-way table
-// slicing from shared memory; slices are combined in a tree with the linear operator "append 2^k
+// chunk, 512 threads: the chunk is staged in shared memory with coalesced 16-byte loads (one padding
+// word per slice keeps the slices in different banks), each thread takes the raw remainder (init 0)
+// of its 128-byte slice byte by byte from a lane-private copy of the 256-entry table; slices are combined in a tree with the linear operator "append 2^k
 // zero bytes" (32x32 bit matrices, precomputed by the host into constant memory).  The chunk is
 // laid out right-aligned in a virtual 64 KiB so every combine step shifts by a fixed amount; the
 // effect of the all-ones initial value, crc_update(0xFFFFFFFF, len zero bytes), is a product of
@@ -24,7 +25,7 @@ namespace sb {
 constexpr uint32_t kCrcPoly = 0x82F63B78u;
 constexpr uint32_t kCrcMaskDelta = 0xa282ead8u;      // framing_format.txt:46-53
 constexpr uint32_t kFrameChunk = 65536;              // :88-91
-constexpr uint32_t kCrcThreads = 256;
+constexpr uint32_t kCrcThreads = 512;
 constexpr uint32_t kFrameIdLen = 10;
 
 struct CrcOps { uint32_t pow[17][32]; };             // pow[k][j] = image of bit j under "append 2^k zero bytes"
@@ -48,10 +49,17 @@ inline void crc_ops_build(CrcOps& o) {               // host, once
 }
 
 __device__ __forceinline__ uint32_t crc_append_zeros(uint32_t v, int k) {   // 2^k zero bytes
-    uint32_t r = 0;
-#pragma unroll 8
-    for (int b = 0; b < 32; ++b) r ^= ((v >> b) & 1u) ? g_crc_ops.pow[k][b] : 0u;
-    return r;
+    // four independent XOR chains: the tree of the CRC kernel waits on this function's latency
+    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+    const uint32_t* m = g_crc_ops.pow[k];
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        r0 ^= (0u - ((v >> b) & 1u)) & m[b];
+        r1 ^= (0u - ((v >> (b + 8)) & 1u)) & m[b + 8];
+        r2 ^= (0u - ((v >> (b + 16)) & 1u)) & m[b + 16];
+        r3 ^= (0u - ((v >> (b + 24)) & 1u)) & m[b + 24];
+    }
+    return (r0 ^ r1) ^ (r2 ^ r3);
 }
 
 struct CrcParams {
@@ -63,66 +71,109 @@ struct CrcParams {
     uint32_t* out_masked;                // masked CRC-32C of chunk c
 };
 
+// Shared-memory image of the chunk: the aligned 16-byte words covering it, one padding word after every
+// slice so that the threads' slices start in different banks.  The byte table is replicated 32 times,
+// entry i of lane l at word 32*i + l: every lane reads its own bank, so a table look-up of the warp is
+// one conflict-free wavefront (a shared 256-entry table serialises ~3.5-fold on random indices).
+constexpr uint32_t kCrcSliceLog = 7;                               // 128-byte slices, 512 threads
+constexpr uint32_t kCrcSlice = 1u << kCrcSliceLog;
+static_assert(kCrcThreads * kCrcSlice == kFrameChunk, "one slice per thread");
+constexpr uint32_t kCrcStageWords = (kFrameChunk + 32) / 4 + (kFrameChunk + 32) / kCrcSlice + 8;
+constexpr uint32_t kCrcSmemBytes = kCrcStageWords * 4 + 256 * 32 * 4 + 2 * kCrcThreads * 4;
+__device__ __forceinline__ uint32_t crc_stage_word(uint32_t y) { return (y >> 2) + (y >> kCrcSliceLog); }   // y % 4 == 0
+
 __global__ void __launch_bounds__(kCrcThreads) crc32c_chunks_kernel(CrcParams p) {
-    __shared__ uint32_t T[4][256];
-    __shared__ uint32_t part[2][kCrcThreads];
-    const uint32_t t = threadIdx.x, c = blockIdx.x;
-    {
-        uint32_t v = t;
+    extern __shared__ __align__(16) uint32_t crc_smem[];
+    uint32_t* sw = crc_smem;                                       // staged chunk
+    uint32_t* T = crc_smem + kCrcStageWords;                       // T[32*i + lane]
+    uint32_t (*part)[kCrcThreads] = reinterpret_cast<uint32_t (*)[kCrcThreads]>(crc_smem + kCrcStageWords + 256 * 32);
+    const uint32_t t = threadIdx.x, lane = t & 31;
+    for (uint32_t i = t >> 5; i < 256; i += kCrcThreads >> 5) {    // warp w fills entries w, w+16, ...: all 32 copies
+        uint32_t v = i;
         for (int b = 0; b < 8; ++b) v = (v >> 1) ^ ((v & 1u) ? kCrcPoly : 0u);
-        T[0][t] = v;
+        T[(i << 5) + lane] = v;
     }
+    // persistent: the table is built once per CTA, chunks are taken round-robin.  Every warp stages
+    // and reads only its own 32 slices (4 KiB of the image), so the warps of a CTA synchronise once
+    // per chunk -- when the 16 warp remainders are merged -- and not between load and compute.
     __syncthreads();
-    {
-        const uint32_t t0 = T[0][t];
-        const uint32_t t1 = (t0 >> 8) ^ T[0][t0 & 0xffu];
-        const uint32_t t2 = (t1 >> 8) ^ T[0][t1 & 0xffu];
-        T[1][t] = t1; T[2][t] = t2; T[3][t] = (t2 >> 8) ^ T[0][t2 & 0xffu];
-    }
-    __syncthreads();
-    const uint64_t off = p.offs ? p.offs[c] : (uint64_t)c * p.stride;
-    uint32_t len;
-    if (p.lens) len = p.lens[c];
-    else { const uint64_t left = p.n_total - off; len = left < p.fixed_len ? (uint32_t)left : p.fixed_len; }
-    if (len > kFrameChunk) len = kFrameChunk;            // callers never ask for more
-    GlobalSrc src{p.base + off};
-    // right-aligned: virtual position v holds data byte v - pad
-    const uint32_t pad = kFrameChunk - len;
-    uint32_t v0 = t * 256u, v1 = v0 + 256u, crc = 0;
-    if (v0 < pad) v0 = pad;
-    if (v0 < v1) {
-        uint32_t i = v0 - pad;
-        const uint32_t e = v1 - pad;
-        for (; ((e - i) & 3u) != 0; ++i)                 // leading bytes: the rest is whole words
-            crc = T[0][(crc ^ __ldg(p.base + off + i)) & 0xffu] ^ (crc >> 8);
-        for (; i + 16 <= e; i += 16) {
-            uint32_t w0, w1, w2, w3;
-            if (i + 20 <= len) src.ld16(i, w0, w1, w2, w3);
-            else { w0 = src.ld32_upto(i, len); w1 = src.ld32_upto(i + 4, len); w2 = src.ld32_upto(i + 8, len); w3 = src.ld32_upto(i + 12, len); }
-            crc ^= w0; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
-            crc ^= w1; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
-            crc ^= w2; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
-            crc ^= w3; crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+    const uint32_t* Tl = T + lane;
+    const uint32_t wid = t >> 5;
+    uint32_t parity = 0;
+    for (uint32_t c = blockIdx.x; c < p.n_chunks; c += gridDim.x, parity ^= 1u) {
+        const uint64_t off = p.offs ? p.offs[c] : (uint64_t)c * p.stride;
+        uint32_t len;
+        if (p.lens) len = p.lens[c];
+        else { const uint64_t left = p.n_total - off; len = left < p.fixed_len ? (uint32_t)left : p.fixed_len; }
+        if (len > kFrameChunk) len = kFrameChunk;        // callers never ask for more
+        const uint8_t* g = p.base + off;
+        const uint32_t skew = (uint32_t)((uintptr_t)g & 15u);
+        // right-aligned: virtual position v holds data byte v - pad = image byte v - pad + skew
+        const uint32_t pad = kFrameChunk - len;
+        uint32_t v0 = t * kCrcSlice, v1 = v0 + kCrcSlice, crc = 0;
+        if (v0 < pad) v0 = pad;
+        {   // the warp's part of the image: whole aligned 16-byte words (a word holding one valid byte
+            // lies in a valid page); neighbouring warps write the same bytes into a shared word
+            uint32_t w0 = wid * 32u * kCrcSlice, w1 = w0 + 32u * kCrcSlice;
+            if (w0 < pad) w0 = pad;
+            if (w0 < w1) {
+                const uint32_t lo16 = (w0 - pad + skew) >> 4, hi16 = (w1 - pad + skew + 15) >> 4;
+                const uint4* g4 = reinterpret_cast<const uint4*>(g - skew);
+#pragma unroll 3
+                for (uint32_t j = lo16 + lane; j < hi16; j += 32) {
+                    const uint4 v = __ldg(g4 + j);
+                    const uint32_t w = crc_stage_word(j << 4);     // 16 bytes never straddle a slice row
+                    sw[w] = v.x; sw[w + 1] = v.y; sw[w + 2] = v.z; sw[w + 3] = v.w;
+                }
+            }
         }
-        for (; i < e; i += 4) {
-            crc ^= src.ld32_upto(i, len);
-            crc = T[3][crc & 0xffu] ^ T[2][(crc >> 8) & 0xffu] ^ T[1][(crc >> 16) & 0xffu] ^ T[0][crc >> 24];
+        __syncwarp();
+        if (v0 < v1) {
+            uint32_t x = v0 - pad + skew;                          // position in the staged image
+            const uint32_t xe = v1 - pad + skew;
+            const uint8_t* sb8 = reinterpret_cast<const uint8_t*>(sw);
+            for (; ((xe - x) & 3u) != 0; ++x)                      // leading bytes: the rest is whole words
+                crc = Tl[((crc ^ sb8[(crc_stage_word(x & ~3u) << 2) + (x & 3u)]) & 0xffu) << 5] ^ (crc >> 8);
+            const uint32_t sh = (x & 3u) << 3;
+            uint32_t y = x & ~3u;
+            uint32_t lo = sw[crc_stage_word(y)];
+            for (; x < xe; x += 4) {
+                y += 4;
+                const uint32_t hi = sw[crc_stage_word(y)];
+                crc ^= __funnelshift_r(lo, hi, sh);
+                lo = hi;
+                crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
+                crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
+                crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
+                crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
+            }
         }
-    }
-    // tree: at level k neighbouring slices of 256 * 2^k bytes merge, left ++ right = shift(left) ^ right
-    part[0][t] = crc;
-    __syncthreads();
-    int cur = 0;
-    for (int k = 0; k < 8; ++k) {
-        const uint32_t pairs = kCrcThreads >> (k + 1);
-        if (t < pairs) part[cur ^ 1][t] = crc_append_zeros(part[cur][2 * t], 8 + k) ^ part[cur][2 * t + 1];
+        __syncwarp();                                              // the image rows may be overwritten by the next chunk
+        // merge: neighbouring runs of kCrcSlice * 2^k bytes, left ++ right = shift(left) ^ right; first
+        // inside the warp (every lane ends with the warp's remainder), then the 16 warps in warp 0
+#pragma unroll 1
+        for (int k = 0; k < 5; ++k) {
+            const uint32_t other = __shfl_xor_sync(kFull, crc, 1u << k);
+            const bool right = (lane >> k) & 1u;
+            crc = crc_append_zeros(right ? other : crc, kCrcSliceLog + k) ^ (right ? crc : other);
+        }
+        if (lane == 0) part[parity][wid] = crc;
         __syncthreads();
-        cur ^= 1;
-    }
-    if (t == 0) {
-        uint32_t init = 0xffffffffu;                     // crc_update(~0, len zero bytes)
-        for (int k = 0; k < 17; ++k) if ((len >> k) & 1u) init = crc_append_zeros(init, k);
-        p.out_masked[c] = crc_mask(~(part[cur][0] ^ init));
+        if (wid == 0) {
+            uint32_t r = part[parity][lane & 15];
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t other = __shfl_xor_sync(kFull, r, 1u << k);
+                const bool right = (lane >> k) & 1u;
+                r = crc_append_zeros(right ? other : r, kCrcSliceLog + 5 + k) ^ (right ? r : other);
+            }
+            if (lane == 0) {
+                uint32_t init = 0xffffffffu;             // crc_update(~0, len zero bytes)
+#pragma unroll 1
+                for (int k = 0; k < 17; ++k) if ((len >> k) & 1u) init = crc_append_zeros(init, k);
+                p.out_masked[c] = crc_mask(~(r ^ init));
+            }
+        }
     }
 }
 

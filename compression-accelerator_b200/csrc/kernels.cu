@@ -369,6 +369,8 @@ cudaError_t kernels_init() {
     e = cudaFuncSetAttribute(decode_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(kStageWarps * (3 * kStageOutMax + 128)));
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCrcSmemBytes);
+    if (e != cudaSuccess) return e;
     static CrcOps ops;                                      // "append 2^k zero bytes" operators of CRC-32C
     crc_ops_build(ops);
     return cudaMemcpyToSymbol(g_crc_ops, &ops, sizeof(ops));
@@ -436,7 +438,8 @@ cudaError_t launch_crc32c_chunks(const uint8_t* base, const unsigned long long* 
     CrcParams p;
     p.base = base; p.offs = offs; p.lens = lens; p.stride = stride; p.n_total = n_total;
     p.fixed_len = fixed_len; p.n_chunks = n_chunks; p.out_masked = out_masked;
-    crc32c_chunks_kernel<<<n_chunks, kCrcThreads, 0, st>>>(p);
+    const uint32_t grid = n_chunks < 2 * 148 ? n_chunks : 2 * 148;   // persistent: two CTAs per SM
+    crc32c_chunks_kernel<<<grid, kCrcThreads, kCrcSmemBytes, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }
