@@ -101,3 +101,68 @@ def test_batch_pages_roundtrip(ctx, oracle):
     l2 = lens2.cpu().numpy()
     assert l2[7] == -1 or l2[7] == 4096          # 0xffffffff, unless the damage happened to stay decodable
     assert (np.delete(l2, 7) == 4096).all()
+
+
+def _pack(streams, stride):
+    """streams (list of bytes) at a fixed stride -> (uint8 array, int32 sizes)."""
+    buf = np.zeros(stride * len(streams) + 64, dtype=np.uint8)
+    for i, s in enumerate(streams):
+        buf[i * stride:i * stride + len(s)] = np.frombuffer(s, dtype=np.uint8)
+    return buf, np.array([len(s) for s in streams], dtype=np.int32)
+
+
+def test_staged_page_kernel_malformed_and_fallback(ctx, oracle):
+    """The page-shaped batch takes decode_staged_kernel (streams and pages staged in shared memory).
+    Every malformed form must be flagged there too, a stream whose preamble promises more than the
+    page capacity is rejected, empty slots are errors, and neighbours are unaffected."""
+    import torch
+    page = 4096
+    text = corpus.fixture("alice29.txt")
+    good = [oracle.compress(text[i * page:(i + 1) * page]) for i in range(24)]
+    fox = oracle.compress(corpus.fixture("fox-in-socks.txt")[:page])
+    bad = [
+        b"",                                              # empty slot
+        b"\x80\x80\x80\x80\x80\x01",                      # varint too long
+        fox[:-1], fox[:len(fox) // 2],                    # truncated
+        fox + b"\x00",                                    # trailing element without data
+        b"\x0a" + bytes([0x01, 0x05]),                    # copy before any output
+        b"\x08\x0cabcd" + bytes([0x01, 0x00]),            # offset 0
+        b"\x04\x0cabcd\x00z",                             # more output than promised
+        b"\x10\x0cabcd",                                  # less output than promised
+        b"\x05" + bytes([61 << 2, 0xff, 0xff]),           # literal longer than the input
+        oracle.compress(text[:page + 1]),                 # decodes to 4097 bytes: larger than the page capacity
+        b"\x06\x0cabcd" + bytes([0x03 | (1 << 2)]) + (2).to_bytes(4, "little"),   # copy-4 form, valid: "abcdcd"
+    ]
+    streams = good[:8] + bad + good[8:]
+    stride = oracle.max_compressed_length(page)
+    buf, sizes = _pack(streams, stride)
+    src = torch.from_numpy(buf).cuda()
+    out, lens = ctx.uncompress_batch_device(src, stride, torch.from_numpy(sizes).cuda(), len(streams), page)
+    ctx.sync()
+    lens = lens.cpu().numpy()
+    out = out.cpu().numpy()
+    for i, s in enumerate(streams):
+        if 8 <= i < 8 + len(bad) - 1:
+            assert lens[i] == -1, (i, lens[i])
+        elif i == 8 + len(bad) - 1:
+            assert lens[i] == 6 and bytes(out[i * page:i * page + 6]) == b"abcdcd"
+        else:
+            j = i if i < 8 else i - len(bad)
+            assert lens[i] == page and bytes(out[i * page:(i + 1) * page]) == text[j * page:(j + 1) * page], i
+
+
+@pytest.mark.parametrize("page,skew", [(1024, 0), (4096, 3), (8192, 1), (100, 5), (16384, 0)])
+def test_batch_page_sizes_and_alignments(ctx, oracle, page, skew):
+    """Staged kernel up to 8 KiB pages, global-memory kernel above; source and destination unaligned."""
+    import torch
+    count = 64
+    text = corpus.fixture("all-mtg-cards.txt")
+    pages = [text[i * page:(i + 1) * page] for i in range(count)]
+    stride = oracle.max_compressed_length(page)
+    buf, sizes = _pack([oracle.compress(p) for p in pages], stride)
+    src = torch.from_numpy(np.concatenate([np.zeros(skew, dtype=np.uint8), buf])).cuda()[skew:]
+    dst = torch.zeros(page * count + skew + 16, dtype=torch.uint8, device="cuda")[skew:]
+    out, lens = ctx.uncompress_batch_device(src, stride, torch.from_numpy(sizes).cuda(), count, page, dst=dst)
+    ctx.sync()
+    assert (lens.cpu().numpy() == page).all()
+    assert bytes(out[:page * count].cpu().numpy()) == b"".join(pages)
