@@ -225,6 +225,14 @@ class Context:
         _check(lib().snappy_b200_uncompress(self._h, data, len(data), out, n.value, C.byref(got)))
         return out.raw[:got.value]
 
+    def uncompress_device(self, src, n, dst, out_n):
+        """Decode the n-byte raw stream in device tensor `src` into `dst`; asynchronous.  out_n (a
+        1-element int64 device tensor) receives the decoded length, or -1 for a malformed stream.
+        Streams of 128 KiB and more are decoded block-parallel when they are block structured."""
+        _check(lib().snappy_b200_uncompress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
+                                                   out_n.data_ptr()))
+        return dst, out_n
+
     def uncompress_batch_device(self, src, in_stride, sizes, count, out_stride, dst=None, out_lens=None):
         """`count` streams at src + i*in_stride (sizes[i] bytes, int32/uint32 device tensor) ->
         (dst, out_lens): stream i decoded at dst + i*out_stride; out_lens[i] = -1 (0xffffffff) if malformed."""

@@ -63,6 +63,7 @@ struct snappy_b200_ctx {
     cudaStream_t stream = nullptr;
     DevBuf seqs, nseq, sizes, offsets, d_in, d_out;
     DevBuf crcs, frame_ix, frame_res;          // framing: per-chunk CRCs, chunk index, walk result + flag
+    DevBuf raw_ix;                             // segment / block index of one large raw stream (decode_par.cuh)
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -351,7 +352,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->seqs.release(); c->nseq.release(); c->sizes.release(); c->offsets.release();
     c->d_in.release(); c->d_out.release();
-    c->crcs.release(); c->frame_ix.release(); c->frame_res.release();
+    c->crcs.release(); c->frame_ix.release(); c->frame_res.release(); c->raw_ix.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -540,14 +541,31 @@ snappy_b200_status snappy_b200_uncompressed_length(const void* src, size_t n, si
     return fail(SNAPPY_B200_INVALID_INPUT, "malformed length preamble");
 }
 
+namespace {
+// One raw stream on the device.  Large streams take the block-parallel path (which falls back to the
+// serial walk on the device when the stream is not block structured); small ones go to one warp.
+constexpr size_t kParDecodeMinBytes = 128u << 10;
+snappy_b200_status decode_one(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst, size_t dst_cap,
+                              unsigned long long* d_out_n) {
+    static const bool par_on = [] { const char* e = getenv("SNAPPY_B200_PAR_DECODE"); return !e || atoi(e) != 0; }();
+    if (par_on && n >= kParDecodeMinBytes) {
+        CU(c->raw_ix.reserve(sb::raw_decode_scratch_bytes(n, dst_cap) + 64));
+        CU(sb::launch_decode_large((const uint8_t*)d_src, n, (uint8_t*)d_dst, dst_cap, c->raw_ix.p, d_out_n,
+                                   c->stream, &c->launches));
+    } else {
+        CU(sb::launch_decode((const uint8_t*)d_src, 0, nullptr, (uint32_t)n, 1, (uint8_t*)d_dst, 0, dst_cap,
+                             nullptr, d_out_n, c->stream, &c->launches));
+    }
+    return SNAPPY_B200_OK;
+}
+}  // namespace
+
 snappy_b200_status snappy_b200_uncompress_device(snappy_b200_ctx* c, const void* d_src, size_t n,
                                                  void* d_dst, size_t dst_cap, unsigned long long* d_out_n) {
     if (!c || !d_src || !d_out_n || (!d_dst && dst_cap)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
     if (n == 0 || n > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "stream length out of range");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    CU(sb::launch_decode((const uint8_t*)d_src, 0, nullptr, (uint32_t)n, 1, (uint8_t*)d_dst, 0, dst_cap,
-                         nullptr, d_out_n, c->stream, &c->launches));
-    return SNAPPY_B200_OK;
+    return decode_one(c, d_src, n, d_dst, dst_cap, d_out_n);
 }
 
 snappy_b200_status snappy_b200_uncompress_batch_device(snappy_b200_ctx* c, const void* d_src,
@@ -575,8 +593,7 @@ snappy_b200_status snappy_b200_uncompress(snappy_b200_ctx* c, const void* src, s
     CU(c->d_in.reserve(n + 64));
     CU(c->d_out.reserve(ulen + 64));
     CU(cudaMemcpyAsync(c->d_in.p, src, n, cudaMemcpyHostToDevice, c->stream));
-    CU(sb::launch_decode((const uint8_t*)c->d_in.p, 0, nullptr, (uint32_t)n, 1, (uint8_t*)c->d_out.p, 0, ulen,
-                         nullptr, c->d_total, c->stream, &c->launches));
+    if (decode_one(c, c->d_in.p, n, c->d_out.p, ulen, c->d_total) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (*c->h_total == ~0ull) return fail(SNAPPY_B200_INVALID_INPUT, "malformed Snappy stream");

@@ -37,6 +37,12 @@ struct DecodeParams {
     const unsigned long long* out_offs = nullptr;
     const uint32_t* caps = nullptr;
     const uint32_t* kinds = nullptr;
+    // decode_par.cuh: blocks of one large stream have no preamble of their own (their decoded length
+    // is caps[j]); the block decode is skipped when *skip_if != 0, the serial walk runs only when
+    // *only_if != 0 -- both flags live on the device, the host never waits to choose
+    uint32_t headerless = 0;
+    const uint32_t* skip_if = nullptr;
+    const uint32_t* only_if = nullptr;
 };
 
 // n bytes d[0..n) = s[0..n), s read-only input (any alignment), all lanes of the warp
@@ -81,11 +87,13 @@ __device__ __forceinline__ void decode_copy(uint8_t* d, uint32_t off, uint32_t n
 
 // One stream, input and output in global memory.  Returns the decoded length or kDecodeError.
 __device__ __forceinline__ uint32_t decode_stream_global(const uint8_t* __restrict__ src, uint32_t n,
-                                                         uint8_t* dst, uint64_t out_cap, uint32_t lane) {
+                                                         uint8_t* dst, uint64_t out_cap, uint32_t lane,
+                                                         bool headerless = false) {
     bool bad = false;
     // varint32 preamble (snappy.cc:1006-1009 on the way in, :864- on the way out)
     uint32_t ip = 0, ulen = 0, shift = 0;
-    for (;;) {
+    if (headerless) ulen = (uint32_t)out_cap;
+    else for (;;) {
         if (ip >= n || shift > 28) { bad = true; break; }
         const uint32_t b = __ldg(src + ip++);
         if (shift == 28 && (b & 0x7fu) > 15u) { bad = true; break; }   // would not fit 32 bits
@@ -146,6 +154,7 @@ __global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (job >= p.n_jobs) return;
+    if ((p.skip_if && *p.skip_if) || (p.only_if && !*p.only_if)) return;
     const uint8_t* __restrict__ src = p.in + (p.in_offs ? p.in_offs[job] : (uint64_t)job * p.in_stride);
     const uint32_t n = p.in_sizes ? p.in_sizes[job] : p.in_size;
     uint8_t* dst = p.out + (p.out_offs ? p.out_offs[job] : (uint64_t)job * p.out_stride);
@@ -155,7 +164,7 @@ __global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
         got = n <= cap ? n : kDecodeError;
         if (got != kDecodeError) decode_literal(dst, src, n, lane);
     } else {
-        got = decode_stream_global(src, n, dst, cap, lane);
+        got = decode_stream_global(src, n, dst, cap, lane, p.headerless != 0);
     }
     if (lane == 0) {
         if (p.out_lens) p.out_lens[job] = got;

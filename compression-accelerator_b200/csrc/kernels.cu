@@ -17,6 +17,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "parse_fast.cuh"
 #include "emit.cuh"
 #include "decode.cuh"
+#include "decode_par.cuh"
 #include "frame.cuh"
 #include <type_traits>
 
@@ -427,6 +428,48 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
         decode_kernel<<<(count + 3) / 4, 128, 0, st>>>(p);
     }
     if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- one large raw stream (decode_par.cuh) ------------------------------------------------------
+static uint64_t raw_segment_bytes(uint64_t n) {      // at least kMinSegment (decode_par.cuh), at most 16 K segments
+    uint64_t s = kMinSegment;
+    while (n / s > 16384) s <<= 1;
+    return s;
+}
+size_t raw_decode_scratch_bytes(uint64_t n, uint64_t out_cap) {
+    const uint64_t seg = raw_segment_bytes(n);
+    return raw_index_bytes((n + seg - 1) / seg, out_cap / kParBlock + 1);
+}
+cudaError_t launch_decode_large(const uint8_t* in, uint64_t n, uint8_t* out, uint64_t out_cap, void* scratch,
+                                unsigned long long* out_len64, cudaStream_t st, unsigned long long* launches) {
+    const uint64_t seg = raw_segment_bytes(n);
+    const uint32_t n_seg = (uint32_t)((n + seg - 1) / seg);
+    const uint64_t n_blk = out_cap / kParBlock + 1;
+    const RawIndex x = raw_index_at(scratch, n_seg, n_blk);
+    cudaError_t e = cudaMemsetAsync(scratch, 0, 64, st);                       // ulen, serial flag
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(x.blk_in, 0xff, n_blk * sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    raw_spec_walk_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, x);
+    raw_exits_kernel<<<1, 1024, 0, st>>>(in, n, seg, n_seg, out_cap, x);
+    raw_sync_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, x);
+    raw_chain_kernel<<<1, 1024, 0, st>>>(n, seg, n_seg, x);
+    raw_blocks_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, n_blk, x);
+    raw_block_table_kernel<<<(uint32_t)((n_blk + 255) / 256), 256, 0, st>>>(n, n_blk, x);
+    DecodeParams p;
+    p.in = in; p.in_stride = 0; p.in_sizes = x.blk_len; p.in_size = 0; p.n_jobs = (uint32_t)n_blk;
+    p.out = out; p.out_stride = 0; p.out_cap = 0; p.out_lens = x.blk_got; p.out_len64 = nullptr;
+    p.in_offs = x.blk_in; p.out_offs = x.blk_out; p.caps = x.blk_cap; p.headerless = 1; p.skip_if = x.serial;
+    decode_kernel<<<(uint32_t)((n_blk + 3) / 4), 128, 0, st>>>(p);
+    raw_verify_kernel<<<(uint32_t)((n_blk + 255) / 256), 256, 0, st>>>(n_blk, x);
+    raw_finish_kernel<<<1, 32, 0, st>>>(x, out_len64);
+    DecodeParams q;                                                             // the hardened serial walk, only if flagged
+    q.in = in; q.in_stride = 0; q.in_sizes = nullptr; q.in_size = (uint32_t)n; q.n_jobs = 1;
+    q.out = out; q.out_stride = 0; q.out_cap = out_cap; q.out_lens = nullptr; q.out_len64 = out_len64;
+    q.only_if = x.serial;
+    decode_kernel<<<1, 128, 0, st>>>(q);
+    if (launches) *launches += 10;
     return cudaGetLastError();
 }
 

@@ -72,6 +72,13 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
                           uint32_t* out_lens, unsigned long long* out_len64, cudaStream_t st,
                           unsigned long long* launches);
 
+// One large raw stream decoded block-parallel when it is block structured, serially otherwise
+// (decode_par.cuh).  `scratch` must hold raw_decode_scratch_bytes(n, out_cap) bytes.  *out_len64 =
+// decoded length or ~0 (malformed).  Asynchronous; the fast/slow decision is made on the device.
+size_t raw_decode_scratch_bytes(uint64_t n, uint64_t out_cap);
+cudaError_t launch_decode_large(const uint8_t* in, uint64_t n, uint8_t* out, uint64_t out_cap, void* scratch,
+                                unsigned long long* out_len64, cudaStream_t st, unsigned long long* launches);
+
 // ---- Snappy framing format (frame.cuh; tests/snappy/framing_format.txt) -------------------------
 // Masked CRC-32C of `n_chunks` chunks of at most 65,536 bytes: chunk c = base + (offs ? offs[c] :
 // c*stride), lens[c] bytes (lens == nullptr: min(fixed_len, n_total - c*stride)).

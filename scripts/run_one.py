@@ -65,6 +65,19 @@ def main():
         tot = int(out_n.item())
         print("%s %s %.1f MiB: parse %.3f ms  gather %.3f ms  %.2f GB/s in, out/in %.4f" % (
             a.data, a.mode, n / 2**20, p, s, n / (p + s) / 1e6, tot / n))
+    if a.decode:
+        import time
+        back = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        got = torch.zeros(1, dtype=torch.int64, device="cuda")
+        ctx.uncompress_device(dst, tot, back, got)
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(a.reps):
+            ctx.uncompress_device(dst, tot, back, got)
+        ctx.sync()
+        ms = (time.perf_counter() - t0) / a.reps * 1e3
+        print("decode one stream of %.1f MiB: %.3f ms  %.2f GB/s out, %.2f GB/s in+out; identical: %s" % (
+            n / 2**20, ms, n / ms / 1e6, (n + tot) / ms / 1e6, bool(int(got.item()) == n and torch.equal(back, src))))
     st = pkg.debug_stats()
     if st[0]:
         f = st[0]

@@ -166,3 +166,109 @@ def test_batch_page_sizes_and_alignments(ctx, oracle, page, skew):
     ctx.sync()
     assert (lens.cpu().numpy() == page).all()
     assert bytes(out[:page * count].cpu().numpy()) == b"".join(pages)
+
+
+# ---- one large raw stream: block-parallel path with on-device fallback (csrc/decode_par.cuh) ----
+def _varint(n):
+    out = bytearray()
+    while n >= 128:
+        out.append((n & 0x7f) | 0x80); n >>= 7
+    out.append(n)
+    return bytes(out)
+
+
+@pytest.mark.parametrize("name,n", [("all-mtg-cards.txt", 3084856), ("alice29.txt", 152089 * 4 + 17),
+                                    ("fireworks.jpeg", 123093 * 3), ("zeros", 5 << 20), ("mtg", 32 << 20)])
+def test_large_stream_parallel_decode(ctx, oracle, name, n):
+    if name == "zeros":
+        data = bytes(n)
+    elif name == "mtg":
+        data = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n).tobytes()
+    else:
+        data = corpus.repeat_to(corpus.fixture(name), n).tobytes()
+    comp = oracle.compress(data)
+    assert len(comp) >= 128 << 10                      # takes the block-parallel path
+    assert ctx.uncompress(comp) == data
+    assert ctx.uncompress(ctx.compress(data, mode="fast")) == data
+
+
+def test_large_stream_not_block_structured_falls_back(ctx, oracle):
+    """Valid streams the fast path must refuse: a copy reaching across a 64 KiB boundary, an element
+    straddling one, one huge literal.  The device-side fallback decodes them all the same."""
+    base = corpus.fixture("all-mtg-cards.txt")[:400000]
+    # (a) literal of everything, then copies that reach far back across block boundaries
+    lit = base
+    L = len(lit) - 1
+    body = bytes([63 << 2]) + L.to_bytes(4, "little") + lit
+    want = bytearray(lit)
+    for off, ln in ((70000, 64), (200000, 33), (65536, 64), (5, 60)):
+        body += bytes([3 | ((ln - 1) << 2)]) + off.to_bytes(4, "little")        # copy-4
+        for _ in range(ln):
+            want.append(want[-off])
+    stream = _varint(len(want)) + body
+    assert len(stream) >= 128 << 10
+    assert ctx.uncompress(stream) == bytes(want)
+    # (b) block-structured stream shifted by a 1000-byte literal in front: elements straddle boundaries
+    tail = oracle.compress(base)
+    hdr_len = len(_varint(len(base)))
+    pre = b"x" * 1000
+    stream = _varint(len(base) + 1000) + bytes([61 << 2]) + (999).to_bytes(2, "little") + pre + tail[hdr_len:]
+    assert ctx.uncompress(stream) == pre + base
+
+
+def test_large_stream_malformed_is_reported(ctx, oracle, pkg):
+    data = corpus.fixture("all-mtg-cards.txt")[:1500000]
+    good = oracle.compress(data)
+    cases = [good[:-1], good[:len(good) // 2], good + b"\x00"]
+    x = bytearray(good); x[300000] ^= 0xff; x[300001] ^= 0xff; x[300002] ^= 0xff
+    cases.append(bytes(x))                                   # may stay decodable: then the bytes must differ or be flagged
+    for i, s in enumerate(cases[:3]):
+        with pytest.raises(pkg.SnappyB200Error):
+            ctx.uncompress(s)
+    try:
+        got = ctx.uncompress(cases[3])
+        assert len(got) == len(data)
+    except pkg.SnappyB200Error:
+        pass
+    # wrong preamble: promises more than the elements deliver
+    bad = _varint(len(data) + 5) + good[len(_varint(len(data))):]
+    with pytest.raises(pkg.SnappyB200Error):
+        ctx.uncompress(bad)
+
+
+def test_large_stream_device_entry_1gib_class(ctx):
+    """256 MiB through the device entries: compress, block-parallel uncompress, compare on the device."""
+    import torch
+    n = 256 << 20
+    src = torch.from_numpy(corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)).cuda()
+    comp, out_n = ctx.compress_device(src)
+    ctx.sync()
+    total = int(out_n.item())
+    back = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    got = torch.zeros(1, dtype=torch.int64, device="cuda")
+    ctx.uncompress_device(comp, total, back, got)
+    ctx.sync()
+    assert int(got.item()) == n and torch.equal(back, src)
+
+
+def test_large_stream_mixed_content(ctx, oracle):
+    """Text, incompressible and constant regions interleaved: long literals (which the speculative
+    walks refuse) next to dense short elements, runs of the true chain spanning several segments."""
+    rng = np.random.default_rng(7)
+    text = corpus.fixture("all-mtg-cards.txt")
+    parts = []
+    for i in range(24):
+        kind = i % 4
+        ln = int(rng.integers(30000, 400000))
+        if kind == 0:
+            parts.append(text[(i * 77777) % 2000000:][:ln])
+        elif kind == 1:
+            parts.append(rng.integers(0, 256, size=ln, dtype=np.uint8).tobytes())
+        elif kind == 2:
+            parts.append(bytes([i]) * ln)
+        else:
+            parts.append(corpus.random_ascii(ln, seed=i).tobytes())
+    data = b"".join(parts)
+    for comp in (oracle.compress(data), ctx.compress(data, mode="fast")):
+        assert len(comp) >= 128 << 10
+        assert ctx.uncompress(comp) == data
