@@ -177,6 +177,17 @@ def next_rows(ctx, src, stream, torch, peak):
                                   "roofline_frac": (n + comp_bytes) / ms / 1e6 / peak,
                                   "identical": bool(torch.equal(back[:n], src))}
     del comp, back
+    # the whole 1 GiB as ONE raw stream (what compress_device just produced): block-parallel decode
+    raw, raw_n = ctx.compress_device(src)
+    torch.cuda.synchronize()
+    raw_total = int(raw_n.item())
+    back = torch.empty(n, dtype=torch.uint8, device=src.device)
+    got = torch.zeros(1, dtype=torch.int64, device=src.device)
+    ms = ev_ms(lambda: ctx.uncompress_device(raw, raw_total, back, got))
+    out["uncompress_one_stream"] = {"value": n / ms / 1e6, "unit": "GB/s decoded", "ms": ms,
+                                    "roofline_frac": (n + raw_total) / ms / 1e6 / peak,
+                                    "identical": bool(int(got.item()) == n and torch.equal(back, src))}
+    del raw, back
     crcs = ctx.crc32c_chunks_device(src)
     ms = ev_ms(lambda: ctx.crc32c_chunks_device(src, out=crcs))
     out["crc32c_64k_chunks"] = {"value": n / ms / 1e6, "unit": "GB/s", "ms": ms, "roofline_frac": n / ms / 1e6 / peak}
