@@ -96,7 +96,11 @@ snappy_b200_status snappy_b200_uncompressed_length(const void* src, size_t n, si
  * SNAPPY_B200_INVALID_INPUT for a malformed stream. */
 snappy_b200_status snappy_b200_uncompress(snappy_b200_ctx* ctx, const void* src, size_t n, void* dst,
                                           size_t dst_cap, size_t* out_n);
-/* Device pointers, asynchronous on the context's stream: *d_out_n = length, or ~0 if malformed. */
+/* Device pointers, asynchronous on the context's stream: *d_out_n = length, or ~0 if malformed.
+ * Streams of 128 KiB and more are decoded block-parallel when they are block structured (an element
+ * starts at every multiple of 65,536 output bytes and no copy reaches across one -- what the
+ * reference compressor and this library produce); any other stream takes the serial walk, decided on
+ * the device.  The result is the same either way. */
 snappy_b200_status snappy_b200_uncompress_device(snappy_b200_ctx* ctx, const void* d_src, size_t n,
                                                  void* d_dst, size_t dst_cap, unsigned long long* d_out_n);
 /* `count` streams: stream i = d_src + i*in_stride, d_sizes[i] bytes, decoded to d_dst + i*out_stride
