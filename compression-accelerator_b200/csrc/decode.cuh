@@ -75,13 +75,14 @@ __device__ __forceinline__ void decode_literal(uint8_t* __restrict__ d, const ui
 }
 
 // n bytes at d[0..n) = the bytes `off` back, pattern-replicated when off < n (snappy.cc:744-790
-// IncrementalCopy).  Reads go to L2 (ld.cg): they fetch what this warp wrote a moment ago.
+// IncrementalCopy).  Plain (L1-cached) loads: the bytes were written by lanes of this same warp, and the
+// __syncwarp() after every element orders those writes before these reads (same CTA: no L1 staleness).
 __device__ __forceinline__ void decode_copy(uint8_t* d, uint32_t off, uint32_t n, uint32_t lane) {
     const uint8_t* s = d - off;
     if (off >= n) {
-        for (uint32_t i = lane; i < n; i += 32) d[i] = __ldcg(s + i);
+        for (uint32_t i = lane; i < n; i += 32) d[i] = s[i];
     } else {
-        for (uint32_t i = lane; i < n; i += 32) d[i] = __ldcg(s + (i % off));
+        for (uint32_t i = lane; i < n; i += 32) d[i] = s[i % off];
     }
 }
 

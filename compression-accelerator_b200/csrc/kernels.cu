@@ -94,7 +94,10 @@ template <bool kGlobal> struct PipeCfg;
 #define SB_PIPE_LEAD 2
 #endif
 template <> struct PipeCfg<false> { static constexpr uint32_t P = 2, R = 8, LEAD = 3; };
-template <> struct PipeCfg<true>  { static constexpr uint32_t P = SB_PIPE_P, R = 8, LEAD = SB_PIPE_LEAD; };
+#ifndef SB_PIPE_R
+#define SB_PIPE_R 8
+#endif
+template <> struct PipeCfg<true>  { static constexpr uint32_t P = SB_PIPE_P, R = SB_PIPE_R, LEAD = SB_PIPE_LEAD; };
 
 template <bool kGlobal>
 __host__ __device__ inline uint32_t pipe_smem_bytes(uint32_t job_len) {
