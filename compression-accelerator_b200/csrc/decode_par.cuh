@@ -34,7 +34,11 @@ namespace sb {
 constexpr uint32_t kSyncW = 256;                 // boundaries recorded at the head of each segment
 constexpr uint32_t kNoBoundary = 0xffffffffu;
 constexpr uint32_t kParBlock = 65536;
-constexpr uint32_t kSpecMaxLiteral = 16384;      // longest literal a speculative walk believes
+constexpr uint32_t kWalkWarps = 2;
+#ifndef SB_SPEC_MAXLIT
+#define SB_SPEC_MAXLIT 4096
+#endif
+constexpr uint32_t kSpecMaxLiteral = SB_SPEC_MAXLIT;   // longest literal a speculative walk believes
 constexpr uint64_t kMinSegment = 2 * kSpecMaxLiteral;
 
 struct RawIndex {
@@ -49,6 +53,7 @@ struct RawIndex {
     unsigned long long* run_delta;               // output bytes from entry_pos to run_exit
     uint32_t* run_end;                           // last segment of the run (the one whose speculative walk is met)
     uint32_t* lead;                              // 1: this segment starts a run of the true chain
+    uint32_t* mlist;                             // segments whose run spans more than themselves, in order
     // per block
     unsigned long long* blk_in;                  // compressed offset of the block's first element (~0: not found)
     unsigned long long* blk_out;                 // 65536 * m
@@ -61,7 +66,7 @@ struct RawIndex {
 };
 
 __host__ __device__ inline size_t raw_index_bytes(uint64_t n_seg, uint64_t n_blk) {
-    return n_seg * (7 * 8 + 2 * 4 + (size_t)kSyncW * 4) + n_blk * (2 * 8 + 3 * 4) + 64;
+    return n_seg * (7 * 8 + 3 * 4 + (size_t)kSyncW * 4) + n_blk * (2 * 8 + 3 * 4) + 64;
 }
 __host__ __device__ inline RawIndex raw_index_at(void* base, uint64_t n_seg, uint64_t n_blk) {
     RawIndex x;
@@ -79,7 +84,8 @@ __host__ __device__ inline RawIndex raw_index_at(void* base, uint64_t n_seg, uin
     x.cum = (uint32_t*)(x.blk_out + n_blk);
     x.run_end = x.cum + n_seg * kSyncW;
     x.lead = x.run_end + n_seg;
-    x.blk_len = x.lead + n_seg;
+    x.mlist = x.lead + n_seg;
+    x.blk_len = x.mlist + n_seg;
     x.blk_cap = x.blk_len + n_blk;
     x.blk_got = x.blk_cap + n_blk;
     return x;
@@ -107,6 +113,26 @@ __device__ __forceinline__ bool raw_element(const uint8_t* __restrict__ s, uint6
     return true;
 }
 
+// The same, without branches: 32 walkers in one warp stay in lockstep (a divergent 4-way tag switch
+// would serialise them).  Reads the two aligned words that hold the tag and up to four length bytes.
+__device__ __forceinline__ bool raw_element_lockstep(const uint8_t* __restrict__ s, uint64_t pos, uint64_t n,
+                                                     uint64_t& esz, uint64_t& olen) {
+    const uintptr_t a = (uintptr_t)(s + pos);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    const uint32_t a0 = __ldg(w);
+    const uint32_t a1 = (reinterpret_cast<const uint8_t*>(w + 1) < s + n) ? __ldg(w + 1) : 0u;
+    const uint64_t q = (((uint64_t)a1 << 32) | a0) >> (((uint32_t)a & 3u) << 3);     // >= 5 bytes from pos
+    const uint32_t tag = (uint32_t)q & 0xffu, kind = tag & 3u, len6 = tag >> 2;
+    const uint32_t extra = max(len6, 59u) - 59u;                                     // 0, or 1..4 length bytes
+    const uint32_t v = (uint32_t)(q >> 8) & (extra ? 0xffffffffu >> (32u - 8u * extra) : 0u);
+    const uint64_t lit = extra ? (uint64_t)v + 1 : (uint64_t)len6 + 1;
+    const uint32_t copy_sz = (0x05030200u >> (8u * kind)) & 0xffu;
+    const uint32_t copy_out = kind == 1 ? 4u + (len6 & 7u) : len6 + 1u;
+    esz = kind ? (uint64_t)copy_sz : 1 + extra + lit;
+    olen = kind ? (uint64_t)copy_out : lit;
+    return kind != 0 || pos + 1 + extra <= n;
+}
+
 __device__ __forceinline__ uint32_t raw_preamble(const uint8_t* __restrict__ s, uint64_t n, uint64_t& ulen) {
     uint32_t ip = 0, shift = 0;
     ulen = 0;
@@ -120,11 +146,11 @@ __device__ __forceinline__ uint32_t raw_preamble(const uint8_t* __restrict__ s, 
     }
 }
 
-// 1. speculative tag walk, one thread per segment
-__global__ void __launch_bounds__(32) raw_spec_walk_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
+// 1. speculative tag walk, one thread per segment, 32 walkers per warp in lockstep
+__global__ void __launch_bounds__(64) raw_spec_walk_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
                                                            uint32_t n_seg, RawIndex x) {
-    const uint32_t k = blockIdx.x;                       // one walker per warp: 32 divergent walks in a warp cost ~8x
-    if (threadIdx.x || k >= n_seg) return;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_seg) return;
     uint32_t* cum = x.cum + (size_t)k * kSyncW;
     for (uint32_t i = 0; i < kSyncW; ++i) cum[i] = kNoBoundary;
     const uint64_t s0 = (uint64_t)k * seg, s1 = s0 + seg < n ? s0 + seg : n;
@@ -137,15 +163,17 @@ __global__ void __launch_bounds__(32) raw_spec_walk_kernel(const uint8_t* __rest
     while (pos < s1) {
         if (pos - s0 < kSyncW) cum[pos - s0] = out < kNoBoundary ? (uint32_t)out : kNoBoundary;
         uint64_t esz, olen;
-        if (!raw_element(s, pos, n, esz, olen)) { pos = n; break; }
+        if (!raw_element_lockstep(s, pos, n, esz, olen)) { pos = n; break; }
         // A long literal is far more often the sign of a walk that is not in step yet (a stray
         // 0xF4/0xF8/0xFC byte read as a tag would send it kilobytes to megabytes away) than a real
         // one.  Speculation only: step one byte and keep looking; a real long literal makes the
         // neighbouring segments part of one run of the true chain, which costs nothing (few, huge
         // elements).  With segments of at least 2 * kSpecMaxLiteral no element a speculative walk
         // accepts can jump over a whole segment.
-        if (k != 0 && olen > kSpecMaxLiteral) { refused = pos + 1; pos += 1; continue; }
-        pos += esz; out += olen;
+        const bool refuse = k != 0 && olen > kSpecMaxLiteral;
+        refused = refuse ? pos + 1 : refused;
+        pos += refuse ? 1 : esz;
+        out += refuse ? 0 : olen;
     }
     x.exit_pos[k] = pos;
     x.spec_out[k] = out;
@@ -199,10 +227,11 @@ __global__ void __launch_bounds__(1024) raw_exits_kernel(const uint8_t* __restri
     }
 }
 
-__global__ void __launch_bounds__(32) raw_sync_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
+__global__ void __launch_bounds__(32 * kWalkWarps) raw_sync_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
                                                       uint32_t n_seg, RawIndex x) {
-    const uint32_t k = blockIdx.x;                       // one walker per warp: 32 divergent walks in a warp cost ~8x
-    if (threadIdx.x || k >= n_seg) return;
+    // one walker per warp (32 divergent walks in one warp cost ~8x), kWalkWarps warps per CTA (32 CTAs per SM at most)
+    const uint32_t k = blockIdx.x * kWalkWarps + (threadIdx.x >> 5);
+    if ((threadIdx.x & 31) || k >= n_seg) return;
     uint64_t pos = x.entry_pos[k], oo = 0;
     uint32_t j = k, end = kRunOpen;
     uint64_t s0 = (uint64_t)j * seg, s1 = s0 + seg < n ? s0 + seg : n;
@@ -233,49 +262,105 @@ __global__ void __launch_bounds__(32) raw_sync_kernel(const uint8_t* __restrict_
     x.run_end[k] = end; x.run_delta[k] = delta; x.run_exit[k] = leave;
 }
 
+// 2c.  Which segments lead a run of the true chain?  Every segment the chain enters (entry inside the
+// segment) leads one, unless it lies inside the run of an earlier leader.  Runs of more than one
+// segment are rare (a speculation that met nothing within its window; an incompressible region), so:
+// collect them in order (parallel compaction), decide among THEM serially which are real (not covered
+// by an earlier real one), clear the segments they cover, check that every leader's run ends where
+// the next entry begins, and turn the leaders' output counts into offsets with a scan.
 __global__ void __launch_bounds__(1024) raw_chain_kernel(uint64_t n, uint64_t seg, uint32_t n_seg, RawIndex x) {
-    __shared__ unsigned long long t_entry[1024], t_exit[1024], t_delta[1024];
-    __shared__ uint32_t t_end[1024], t_lead[1024];
-    __shared__ unsigned long long c_e, c_o;
-    __shared__ uint32_t c_skip_to, c_bad;
-    const uint32_t t = threadIdx.x;
-    if (t == 0) { c_e = x.entry_pos[0]; c_o = 0; c_skip_to = 0; c_bad = 0; }
+    __shared__ unsigned long long warp_sum[32];
+    __shared__ unsigned long long carry_s;
+    __shared__ uint32_t warp_cnt[32];
+    __shared__ uint32_t m_count, bad, last_leader;
+    const uint32_t t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    if (t == 0) { m_count = 0; bad = 0; carry_s = 0; last_leader = 0; }
     __syncthreads();
+    // A: entered segments are tentative leaders; multi-segment runs are listed in order
     for (uint32_t base = 0; base < n_seg; base += 1024) {
         const uint32_t k = base + t;
+        bool entered = false, multi = false;
         if (k < n_seg) {
-            t_entry[t] = x.entry_pos[k]; t_exit[t] = x.run_exit[k]; t_delta[t] = x.run_delta[k]; t_end[t] = x.run_end[k];
+            const uint64_t s0 = (uint64_t)k * seg, s1 = s0 + seg < n ? s0 + seg : n;
+            entered = x.entry_pos[k] < s1;
+            multi = entered && x.run_end[k] != k;
+            x.lead[k] = entered ? 1u : 0u;
         }
+        const uint32_t bal = __ballot_sync(kFull, multi);
+        if (lane == 0) warp_cnt[wid] = __popc(bal);
         __syncthreads();
-        if (t == 0) {
-            uint64_t e = c_e, o = c_o;
-            uint32_t skip_to = c_skip_to, bad = c_bad;
-            const uint32_t cnt = n_seg - base < 1024 ? n_seg - base : 1024;
-            for (uint32_t i = 0; i < cnt; ++i) {
-                const uint32_t kk = base + i;
-                const uint64_t s0 = (uint64_t)kk * seg, s1 = s0 + seg < n ? s0 + seg : n;
-                t_lead[i] = 0;
-                if (kk < skip_to || e >= s1) continue;                   // inside a run / spanned by an element
-                if (t_entry[i] != e || t_end[i] == kRunOpen) { bad = 1; break; }
-                t_lead[i] = 1;
-                t_entry[i] = o;                                          // becomes entry_out
-                o += t_delta[i]; e = t_exit[i]; skip_to = t_end[i] + 1;
-            }
-            c_e = e; c_o = o; c_skip_to = skip_to; c_bad = bad;
-        }
+        uint32_t before = 0;
+        for (uint32_t w = 0; w < wid; ++w) before += warp_cnt[w];
+        if (multi) x.mlist[m_count + before + __popc(bal & ((1u << lane) - 1u))] = k;
         __syncthreads();
-        if (k < n_seg) { x.lead[k] = t_lead[t]; if (t_lead[t]) x.entry_out[k] = t_entry[t]; }
+        if (t == 0) { uint32_t tot = 0; for (uint32_t w = 0; w < 32; ++w) tot += warp_cnt[w]; m_count += tot; }
         __syncthreads();
-        if (c_bad) break;
     }
-    if (t == 0 && (c_bad || c_e != n || c_o != *x.ulen)) *x.serial = 1;
+    // B: among the multi-segment runs, in order, the real ones are those not inside an earlier real one
+    if (t == 0) {
+        uint32_t covered_until = 0;                      // segments below this index are inside a real run
+        for (uint32_t i = 0; i < m_count; ++i) {
+            const uint32_t k = x.mlist[i];
+            if (k < covered_until) { x.mlist[i] = kRunOpen; continue; }       // a walk from a wrong entry
+            const uint32_t e = x.run_end[k];
+            if (e == kRunOpen) { bad = 1; break; }
+            covered_until = e + 1;
+        }
+    }
+    __syncthreads();
+    // C: segments inside a real multi-segment run do not lead
+    for (uint32_t i = wid; i < m_count && !bad; i += 32) {
+        const uint32_t k = x.mlist[i];
+        if (k == kRunOpen) continue;
+        const uint32_t e = x.run_end[k];
+        for (uint32_t j = k + 1 + lane; j <= e && j < n_seg; j += 32) x.lead[j] = 0;
+    }
+    __syncthreads();
+    // D: every leader's run must end where the next entry begins; E: offsets
+    for (uint32_t base = 0; base < n_seg && !bad; base += 1024) {
+        const uint32_t k = base + t;
+        unsigned long long v = 0;
+        if (k < n_seg && x.lead[k]) {
+            const uint32_t e = x.run_end[k];
+            if (e == kRunOpen) bad = 1;
+            else {
+                const uint64_t leave = x.run_exit[k];
+                if (e + 1 < n_seg ? x.entry_pos[e + 1] != leave : leave != n) bad = 1;
+                v = x.run_delta[k];
+                atomicMax(&last_leader, k);
+            }
+        }
+        unsigned long long xs = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long y = __shfl_up_sync(kFull, xs, d);
+            if (lane >= (uint32_t)d) xs += y;
+        }
+        if (lane == 31) warp_sum[wid] = xs;
+        __syncthreads();
+        if (wid == 0) {
+            unsigned long long sv = warp_sum[lane], tv = sv;
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long y = __shfl_up_sync(kFull, tv, d);
+                if (lane >= (uint32_t)d) tv += y;
+            }
+            warp_sum[lane] = tv - sv;
+        }
+        __syncthreads();
+        const unsigned long long excl = carry_s + warp_sum[wid] + (xs - v);
+        if (k < n_seg) x.entry_out[k] = excl;
+        __syncthreads();
+        if (t == 1023) carry_s = excl + v;
+        __syncthreads();
+    }
+    // the last run must leave exactly at the end of the stream (segments after it are spanned by its last element)
+    if (t == 0 && (bad || carry_s != *x.ulen || x.run_exit[last_leader] != n)) *x.serial = 1;
 }
 
-// 3. compressed offset of every 64 KiB block: the leader of a run walks the whole run
-__global__ void __launch_bounds__(32) raw_blocks_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
+// 3. compressed offset of every 64 KiB block: the leader of a run walks the whole run (lockstep, as 1.)
+__global__ void __launch_bounds__(64) raw_blocks_kernel(const uint8_t* __restrict__ s, uint64_t n, uint64_t seg,
                                                         uint32_t n_seg, uint64_t n_blk, RawIndex x) {
-    const uint32_t k = blockIdx.x;                       // one walker per warp: 32 divergent walks in a warp cost ~8x
-    if (threadIdx.x || k >= n_seg || *x.serial || !x.lead[k]) return;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_seg || *x.serial || !x.lead[k]) return;
     const uint64_t stop = x.run_exit[k];
     uint64_t pos = x.entry_pos[k], o = x.entry_out[k];
     while (pos < stop) {
@@ -284,7 +369,7 @@ __global__ void __launch_bounds__(32) raw_blocks_kernel(const uint8_t* __restric
             if (m < n_blk) x.blk_in[m] = pos;
         }
         uint64_t esz, olen;
-        if (!raw_element(s, pos, n, esz, olen)) { *x.serial = 1; return; }
+        if (!raw_element_lockstep(s, pos, n, esz, olen)) { *x.serial = 1; return; }
         if ((o & (kParBlock - 1)) + olen > kParBlock) { *x.serial = 1; return; }   // element straddles a block
         pos += esz; o += olen;
     }

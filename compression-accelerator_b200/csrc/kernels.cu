@@ -437,7 +437,7 @@ cudaError_t launch_decode(const uint8_t* in, uint64_t in_stride, const uint32_t*
 // ---- one large raw stream (decode_par.cuh) ------------------------------------------------------
 static uint64_t raw_segment_bytes(uint64_t n) {      // at least kMinSegment (decode_par.cuh), at most 16 K segments
     uint64_t s = kMinSegment;
-    while (n / s > 16384) s <<= 1;
+    while (n / s > 65536) s <<= 1;
     return s;
 }
 size_t raw_decode_scratch_bytes(uint64_t n, uint64_t out_cap) {
@@ -454,11 +454,11 @@ cudaError_t launch_decode_large(const uint8_t* in, uint64_t n, uint8_t* out, uin
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(x.blk_in, 0xff, n_blk * sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
-    raw_spec_walk_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, x);
+    raw_spec_walk_kernel<<<(n_seg + 63) / 64, 64, 0, st>>>(in, n, seg, n_seg, x);
     raw_exits_kernel<<<1, 1024, 0, st>>>(in, n, seg, n_seg, out_cap, x);
-    raw_sync_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, x);
+    raw_sync_kernel<<<(n_seg + kWalkWarps - 1) / kWalkWarps, 32 * kWalkWarps, 0, st>>>(in, n, seg, n_seg, x);
     raw_chain_kernel<<<1, 1024, 0, st>>>(n, seg, n_seg, x);
-    raw_blocks_kernel<<<n_seg, 32, 0, st>>>(in, n, seg, n_seg, n_blk, x);
+    raw_blocks_kernel<<<(n_seg + 63) / 64, 64, 0, st>>>(in, n, seg, n_seg, n_blk, x);
     raw_block_table_kernel<<<(uint32_t)((n_blk + 255) / 256), 256, 0, st>>>(n, n_blk, x);
     DecodeParams p;
     p.in = in; p.in_stride = 0; p.in_sizes = x.blk_len; p.in_size = 0; p.n_jobs = (uint32_t)n_blk;
