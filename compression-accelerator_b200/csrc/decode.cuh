@@ -151,7 +151,10 @@ __device__ __forceinline__ uint32_t decode_stream_global(const uint8_t* __restri
     return bad ? kDecodeError : op;
 }
 
-__global__ void __launch_bounds__(128) decode_kernel(DecodeParams p) {
+#ifndef SB_DECODE_MINB
+#define SB_DECODE_MINB 16                // 32 registers: 64 warps per SM (the walk is latency bound)
+#endif
+__global__ void __launch_bounds__(128, SB_DECODE_MINB) decode_kernel(DecodeParams p) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (job >= p.n_jobs) return;
