@@ -202,6 +202,83 @@ def next_rows(ctx, src, stream, torch, peak):
     return out
 
 
+def config_rows(ctx, pkg, stream, torch, peak):
+    """The other configurations BASELINE.json names, exact mode, measured
+    with CUDA events on the library's stream, device-resident.  The file configurations are checked
+    against the committed golden manifest (sha256 of the reference Snappy's stream); the batch
+    configuration through the device decompressor.  Reported beside the headline; not part of `value`."""
+    import hashlib
+    import numpy as np
+    import corpus
+    dev = torch.device("cuda", torch.cuda.current_device())
+    man = corpus.manifest()["files"]
+
+    def ev_ms(fn, reps=5):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    out = {}
+    # configs[0], [1], [2]: the reference's data files as they are (1, 48 and 2 fragments)
+    for key, name in (("fox_in_socks", "fox-in-socks.txt"), ("all_mtg_cards", "all-mtg-cards.txt"),
+                      ("randomASCII", "randomASCII.txt")):
+        data = corpus.fixture(name)
+        n = len(data)
+        src = torch.from_numpy(np.frombuffer(data, dtype=np.uint8).copy()).to(dev)
+        dst, out_n = ctx.compress_device(src)
+        ms = ev_ms(lambda: ctx.compress_device(src, dst, out_n), reps=20)
+        total = int(out_n.item())
+        got = bytes(dst[:total].cpu().numpy())
+        t0 = time.perf_counter()
+        for _ in range(20):
+            ctx.compress(data)
+        host_us = (time.perf_counter() - t0) / 20 * 1e6
+        out[key] = {"bytes": n, "fragments": -(-n // 65536), "compressed_bytes": total,
+                    "device_us": ms * 1e3, "host_call_us": host_us, "value": n / ms / 1e6, "unit": "GB/s",
+                    "identical_to_reference": hashlib.sha256(got).hexdigest() == man[name]["sha256"]}
+    # configs[2] scaled: 1 GiB uniform over the same 93 symbols (literal-dominated path)
+    n = GIB
+    src = torch.from_numpy(corpus.random_ascii(n)).to(dev)
+    dst, out_n = ctx.compress_device(src)
+    ms = ev_ms(lambda: ctx.compress_device(src, dst, out_n))
+    total = int(out_n.item())
+    back = torch.empty(n, dtype=torch.uint8, device=dev)
+    got_n = torch.zeros(1, dtype=torch.int64, device=dev)
+    ctx.uncompress_device(dst, total, back, got_n)
+    torch.cuda.synchronize()
+    out["random_ascii_1gib"] = {"bytes": n, "compressed_bytes": total, "ms": ms, "value": n / ms / 1e6,
+                                "unit": "GB/s", "roofline_frac": (n + total) / ms / 1e6 / peak,
+                                "round_trip": bool(int(got_n.item()) == n and torch.equal(back, src))}
+    del dst, back
+    # configs[3]: 1,048,576 independent 4 KiB buffers, each its own Snappy stream; three families
+    page, count = 4096, 1 << 20
+    text = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), GIB)
+    fam = {"real": lambda: torch.from_numpy(text).to(dev).repeat(4),
+           "random": lambda: src.repeat(4),
+           "repeating": lambda: torch.full((page * count,), 97, dtype=torch.uint8, device=dev)}
+    pages = {}
+    for kind, make in fam.items():
+        buf = make()
+        comp, ostride, sizes = ctx.compress_batch_device(buf, page, page, count)
+        ms = ev_ms(lambda: ctx.compress_batch_device(buf, page, page, count, dst=comp, sizes=sizes), reps=3)
+        comp_bytes = int(sizes.sum().item())
+        back, lens = ctx.uncompress_batch_device(comp, ostride, sizes, count, page)
+        torch.cuda.synchronize()
+        pages[kind] = {"ms": ms, "value": page * count / ms / 1e6, "unit": "GB/s", "compressed_bytes": comp_bytes,
+                       "roofline_frac": (page * count + comp_bytes) / ms / 1e6 / peak,
+                       "round_trip": bool(torch.equal(back[:page * count], buf) and bool((lens == page).all()))}
+        del buf, comp, back, sizes, lens
+    out["pages_1m_x_4k"] = pages
+    return out
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -322,21 +399,26 @@ def run_ours(args):
         dist.all_reduce(e2e_o, op=dist.ReduceOp.MAX)
     mode_now[0] = args.mode
 
-    extra = None
+    extra = cfg_rows = None
     if rank == 0 and world == 1:
         try:
             extra = next_rows(ctx, src, stream, torch, measured_peak()[0])
         except Exception as e:                     # never lose the headline line to a side measurement
             extra = {"error": repr(e)}
+        try:
+            cfg_rows = config_rows(ctx, pkg, stream, torch, measured_peak()[0])
+        except Exception as e:
+            cfg_rows = {"error": repr(e)}
     if rank == 0:
         peak, peak_src = measured_peak()
         pms = sorted(parse_ms)[len(parse_ms) // 2]
         gms = sorted(gather_ms)[len(gather_ms) // 2]
         algo = n + comp_n
         ach = algo / (pms * 1e-3) / 1e9
-        cpu = cpu_reference(host, os.cpu_count() or 1)
-        cpu1 = cpu_reference(host, 1, budget_s=6.0)
-        cpu["single_thread_GBps"] = cpu1["value"]
+        cpu = None
+        if world == 1:                             # the CPU baseline is an N=1 row (rank 0's host cores)
+            cpu = cpu_reference(host, os.cpu_count() or 1)
+            cpu["single_thread_GBps"] = cpu_reference(host, 1, budget_s=6.0)["value"]
         line = {
             "metric": "snappy_compress_input_GBps", "value": world * n * args.steps / (ms * 1e-3) / 1e9,
             "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -365,7 +447,7 @@ def run_ours(args):
                            "parse_kernel_ms": sorted(o_parse)[1],
                            "roofline_frac": (n + comp_o) / (sorted(o_parse)[1] * 1e-3) / 1e9 / peak,
                            "traffic": measured_traffic(other)},
-            "next_rows": extra,
+            "next_rows": extra, "config_rows": cfg_rows,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -30,6 +30,9 @@ constexpr uint32_t kDone = 0xffffffffu;
 #ifndef SB_PIPE_SLEEP
 #define SB_PIPE_SLEEP 100
 #endif
+#ifndef SB_PIPE_PREFETCH
+#define SB_PIPE_PREFETCH 0               // resolver fetches the next window's record ahead of its commit
+#endif
 
 // ---- input accessors ------------------------------------------------------------------------
 struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
@@ -297,20 +300,31 @@ struct PipeResolver {
         const uint32_t lt = (1u << lane) - 1u;
         uint32_t win = 0, sl = 1, I = 0;
         int scan0 = 1;
+#if SB_PIPE_PREFETCH
+        uint4 pre_rec = make_uint4(0, 0, 0, 0), pre_hdr = make_uint4(0, 0, 0, 0);
+        uint32_t pre_win = kDone;                            // window whose record sits in pre_rec/pre_hdr
+#endif
         for (;;) {
             // ---- take the producer's record of this window, validate the speculation ----------
             const uint32_t wbase = win << 5, pos = wbase + lane, si = win % R;
 #ifdef SNAPPY_B200_STATS
             const long long t0 = clock64();
 #endif
-            for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
-                if (spins > (1u << 24)) __trap();            // watchdog: never hang the GPU
+            uint4 rec, hdr;
+#if SB_PIPE_PREFETCH
+            if (pre_win == win) { rec = pre_rec; hdr = pre_hdr; }
+            else
+#endif
+            {
+                for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
+                    if (spins > (1u << 24)) __trap();        // watchdog: never hang the GPU
+                __syncwarp();
+                rec = ps->rec[si][lane];
+                hdr = ps->hdr[si];
+            }
 #ifdef SNAPPY_B200_STATS
             st_wait += clock64() - t0; ++st_win;
 #endif
-            __syncwarp();
-            const uint4 rec = ps->rec[si][lane];
-            const uint4 hdr = ps->hdr[si];
             const uint32_t h = rec.x & 0xffffu;
             uint32_t T;                                      // exact: earlier windows are committed
             {
@@ -383,6 +397,21 @@ struct PipeResolver {
                 }
                 uint32_t ip = 0;
                 bool jump = false, e32 = false;        // e32: the copy ended exactly at the window end
+#if SB_PIPE_PREFETCH
+                {   // the next window's record is usually complete by now: fetch it under the commit and
+                    // publish below (flag first, then the record; shared-memory loads of a warp stay in order)
+                    const uint32_t s1 = (win + 1) % R;
+                    uint32_t rdy;
+                    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(rdy) : "r"(smem_u32(const_cast<const uint32_t*>(&ps->ready[s1]))) : "memory");
+                    asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(pre_rec.x), "=r"(pre_rec.y), "=r"(pre_rec.z), "=r"(pre_rec.w)
+                                 : "r"(smem_u32(&ps->rec[s1][lane])) : "memory");
+                    asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(pre_hdr.x), "=r"(pre_hdr.y), "=r"(pre_hdr.z), "=r"(pre_hdr.w)
+                                 : "r"(smem_u32(&ps->hdr[s1])) : "memory");
+                    pre_win = rdy == win + 2 ? win + 1 : kDone;
+                }
+#endif
                 if (f == 32) {
                     const uint32_t vend = chosen ? 32u : vend0;
                     const uint32_t upto = vend < vpre_end ? vend : vpre_end;
