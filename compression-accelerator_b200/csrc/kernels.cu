@@ -27,13 +27,8 @@ namespace sb {
 constexpr uint32_t kSmemTableOff = 128;
 constexpr uint32_t kInputPad = 32;   // slack so unaligned word reads past the end stay in bounds
 
-// peer-detector scratch (parse_window.cuh): fewer slots for small jobs so more of them fit an SM
-__host__ __device__ inline uint32_t peer_slots(uint32_t job_len) {
-    return job_len > 16384 ? kPeerSlots : 512u;
-}
 __host__ __device__ inline uint32_t parse_smem_bytes(uint32_t job_len) {
-    return kSmemTableOff + table_entries(job_len) * 2 + peer_slots(job_len) * 4 +
-           ((job_len + 15u) & ~15u) + kInputPad;
+    return kSmemTableOff + table_entries(job_len) * 2 + ((job_len + 15u) & ~15u) + kInputPad;
 }
 
 // Stage src[0,len) into shared memory: TMA bulk copy for the 16-byte-aligned body, ordinary
@@ -70,14 +65,11 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     uint16_t* table = reinterpret_cast<uint16_t*>(smem + kSmemTableOff);
     const uint32_t len = job_len_of(p, job);
     const uint32_t entries = table_entries(len);            // from THIS fragment's length
-    uint32_t* scr = reinterpret_cast<uint32_t*>(smem + kSmemTableOff + table_entries(p.job_len) * 2);
-    const uint32_t nscr = peer_slots(p.job_len);
-    uint8_t* s_in = reinterpret_cast<uint8_t*>(scr + nscr);
-    if (kWindow) for (uint32_t i = lane; i < nscr; i += 32) scr[i] = kFull;
+    uint8_t* s_in = smem + kSmemTableOff + table_entries(p.job_len) * 2;
     stage_fragment(p.in + (uint64_t)job * p.in_stride, len, s_in, table, entries, bar, lane);
     SeqWriter out{p.seqs + (uint64_t)job * seq_stride(p.job_len), 0};
     const int shift = 32 - (31 - __clz(entries));           // snappy.cc:548
-    if (kWindow) parse_fragment_window(s_in, len, table, scr, nscr - 1, shift, out, lane);
+    if (kWindow) parse_fragment_window(SmemSrc{s_in}, len, table, shift, out, lane);
     else parse_fragment_serial(s_in, len, table, shift, out, lane);
     if (lane == 0) p.nseq[job] = out.n;
 }
@@ -87,6 +79,9 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
 // kGlobal = true : producers gather the input from global memory; shared memory holds only the
 //                  table and the ring (up to 6 fragments per SM).
 template <bool kGlobal> struct PipeCfg;
+#ifndef SB_PIPE_MIN_LEN
+#define SB_PIPE_MIN_LEN 8192             // jobs up to this length take the single-warp parser
+#endif
 #ifndef SB_PIPE_P
 #define SB_PIPE_P 4
 #endif
@@ -387,7 +382,7 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
         const uint32_t K = fast_evaluators(p.job_len);      // 14 -> the 16-warp CTA (12 of them evaluate)
         parse_fast_kernel<<<p.n_jobs, 32 * (2 + K), fast_layout(p.job_len).total, st>>>(p);
     } else if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
-    else if (mode == 0 && p.job_len > 16384)   // small jobs fit many per SM: the single-warp parser wins
+    else if (mode == 0 && p.job_len > SB_PIPE_MIN_LEN)   // small jobs fit many per SM: the single-warp parser wins
         parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
     else if (mode == 4)
         parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);

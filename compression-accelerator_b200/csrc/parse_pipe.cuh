@@ -30,92 +30,6 @@ constexpr uint32_t kDone = 0xffffffffu;
 #ifndef SB_PIPE_SLEEP
 #define SB_PIPE_SLEEP 100
 #endif
-#ifndef SB_PIPE_PREFETCH
-#define SB_PIPE_PREFETCH 0               // resolver fetches the next window's record ahead of its commit
-#endif
-
-// ---- input accessors ------------------------------------------------------------------------
-struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
-    const uint8_t* s;
-    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const { return lds32u(s, pos); }
-    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t) const { return lds32u(s, pos); }
-    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
-                                         uint32_t& b3) const { lds16u(s, pos, b0, b1, b2, b3); }
-};
-
-struct GlobalSrc {                       // fragment read in place from global memory
-    const uint8_t* g;                    // fragment start (any alignment)
-    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const {
-        const uintptr_t a = (uintptr_t)(g + pos);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-        const uint32_t sh = ((uint32_t)a & 3u) << 3;
-        const uint32_t a0 = __ldg(w), a1 = sh ? __ldg(w + 1) : 0u;
-        return __funnelshift_r(a0, a1, sh);
-    }
-    // as ld32, but never touches a word that lies entirely at or beyond position `end` (the
-    // last fragment may end on the last mapped byte of the caller's buffer)
-    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t end) const {
-        const uintptr_t a = (uintptr_t)(g + pos);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-        const uint32_t r = (uint32_t)a & 3u;
-        const uint32_t a0 = __ldg(w), a1 = (r && pos + 4 - r < end) ? __ldg(w + 1) : 0u;
-        return __funnelshift_r(a0, a1, r << 3);
-    }
-    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
-                                         uint32_t& b3) const {
-        const uintptr_t a = (uintptr_t)(g + pos);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-        const uint32_t sh = ((uint32_t)a & 3u) << 3;
-        const uint32_t a0 = __ldg(w), a1 = __ldg(w + 1), a2 = __ldg(w + 2), a3 = __ldg(w + 3);
-        const uint32_t a4 = sh ? __ldg(w + 4) : 0u;         // never touch a word without needed bytes
-        b0 = __funnelshift_r(a0, a1, sh);
-        b1 = __funnelshift_r(a1, a2, sh);
-        b2 = __funnelshift_r(a2, a3, sh);
-        b3 = __funnelshift_r(a3, a4, sh);
-    }
-};
-
-// FindMatchLength (snappy-internal.h:95-143) over an accessor, 128 bytes per round.
-template <class Src>
-__device__ __forceinline__ uint32_t src_match_len(const Src& src, uint32_t a, uint32_t b,
-                                                  uint32_t end, int lane) {
-    uint32_t n = 0;
-    for (;;) {
-        const uint32_t pb = b + n + (lane << 2);
-        uint32_t m = 0;
-        if (pb < end) {
-            const uint32_t x = src.ld32_upto(a + n + (lane << 2), end) ^ src.ld32_upto(pb, end);
-            m = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
-            m = min(m, end - pb);
-        }
-        const uint32_t bal = __ballot_sync(kFull, m < 4);
-        if (bal) {
-            const int first = __ffs(bal) - 1;
-            return n + (first << 2) + __shfl_sync(kFull, m, first);
-        }
-        n += 128;
-    }
-}
-
-// Serial scan (snappy.cc:587-608) over an accessor; see parse_serial.cuh.
-template <class Src>
-__device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table, int shift,
-                                                uint32_t ip_limit, uint32_t& ip, uint32_t& skip,
-                                                uint32_t& cand) {
-    uint32_t nxt = ip;
-    for (;;) {
-        ip = nxt;
-        const uint32_t step = skip >> 5;
-        skip += step;
-        nxt = ip + step;
-        if (nxt > ip_limit) return false;
-        const uint32_t w = src.ld32(ip);
-        const uint32_t h = hash32(w, shift);
-        cand = table[h];
-        table[h] = (uint16_t)ip;
-        if (src.ld32(cand) == w) return true;
-    }
-}
 
 // Slow-path probe of position p against candidate cand in ONE round trip: lane 0 compares the
 // 4-byte words (snappy.cc:607), lanes 1..31 the following 124 bytes (FindMatchLength).  Returns 0
@@ -300,31 +214,20 @@ struct PipeResolver {
         const uint32_t lt = (1u << lane) - 1u;
         uint32_t win = 0, sl = 1, I = 0;
         int scan0 = 1;
-#if SB_PIPE_PREFETCH
-        uint4 pre_rec = make_uint4(0, 0, 0, 0), pre_hdr = make_uint4(0, 0, 0, 0);
-        uint32_t pre_win = kDone;                            // window whose record sits in pre_rec/pre_hdr
-#endif
         for (;;) {
             // ---- take the producer's record of this window, validate the speculation ----------
             const uint32_t wbase = win << 5, pos = wbase + lane, si = win % R;
 #ifdef SNAPPY_B200_STATS
             const long long t0 = clock64();
 #endif
-            uint4 rec, hdr;
-#if SB_PIPE_PREFETCH
-            if (pre_win == win) { rec = pre_rec; hdr = pre_hdr; }
-            else
-#endif
-            {
-                for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
-                    if (spins > (1u << 24)) __trap();        // watchdog: never hang the GPU
-                __syncwarp();
-                rec = ps->rec[si][lane];
-                hdr = ps->hdr[si];
-            }
+            for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
+                if (spins > (1u << 24)) __trap();            // watchdog: never hang the GPU
 #ifdef SNAPPY_B200_STATS
             st_wait += clock64() - t0; ++st_win;
 #endif
+            __syncwarp();
+            const uint4 rec = ps->rec[si][lane];
+            const uint4 hdr = ps->hdr[si];
             const uint32_t h = rec.x & 0xffffu;
             uint32_t T;                                      // exact: earlier windows are committed
             {
@@ -397,21 +300,6 @@ struct PipeResolver {
                 }
                 uint32_t ip = 0;
                 bool jump = false, e32 = false;        // e32: the copy ended exactly at the window end
-#if SB_PIPE_PREFETCH
-                {   // the next window's record is usually complete by now: fetch it under the commit and
-                    // publish below (flag first, then the record; shared-memory loads of a warp stay in order)
-                    const uint32_t s1 = (win + 1) % R;
-                    uint32_t rdy;
-                    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(rdy) : "r"(smem_u32(const_cast<const uint32_t*>(&ps->ready[s1]))) : "memory");
-                    asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                                 : "=r"(pre_rec.x), "=r"(pre_rec.y), "=r"(pre_rec.z), "=r"(pre_rec.w)
-                                 : "r"(smem_u32(&ps->rec[s1][lane])) : "memory");
-                    asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                                 : "=r"(pre_hdr.x), "=r"(pre_hdr.y), "=r"(pre_hdr.z), "=r"(pre_hdr.w)
-                                 : "r"(smem_u32(&ps->hdr[s1])) : "memory");
-                    pre_win = rdy == win + 2 ? win + 1 : kDone;
-                }
-#endif
                 if (f == 32) {
                     const uint32_t vend = chosen ? 32u : vend0;
                     const uint32_t upto = vend < vpre_end ? vend : vpre_end;

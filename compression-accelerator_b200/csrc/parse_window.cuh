@@ -12,7 +12,7 @@
 // Exactness.  A probe's candidate is the most recent insert with its hash.  Inserts of earlier
 // windows are in the table when a window is entered.  Inserts made inside the window can only
 // shadow the table entry of a lane that shares its hash with a lower lane ("peer" lanes, found
-// with a shared-memory min-scatter); those lanes, and matches longer than the 12 pre-extended
+// with match.any -- a shared-memory min-scatter was no faster and its scratch cost two pages per SM); those lanes, and matches longer than the 12 pre-extended
 // bytes, are evaluated exactly when the chase reaches them (slow path).  Table inserts (:606,
 // :649-655) are kept as a lane mask and committed when the parse leaves the window, the highest
 // lane per slot winning as in serial order.  Scans that miss 32 times in a row (skip >= 64,
@@ -22,7 +22,6 @@
 
 namespace sb {
 
-constexpr uint32_t kPeerSlots = 2048;   // uint32 scratch slots of the peer detector (stream path)
 
 // five aligned words starting at the word containing `pos` -> the 16 bytes at pos..pos+15
 __device__ __forceinline__ void lds16u(const uint8_t* s, uint32_t pos, uint32_t& b0, uint32_t& b1,
@@ -39,6 +38,89 @@ __device__ __forceinline__ void lds16u(const uint8_t* s, uint32_t pos, uint32_t&
 // one SHF each: the funnel shift clamps the count at 32
 __device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return __funnelshift_lc(0u, kFull, s); }
 __device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return __funnelshift_lc(kFull, 0u, e); }
+
+// ---- input accessors ------------------------------------------------------------------------
+struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
+    const uint8_t* s;
+    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const { return lds32u(s, pos); }
+    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t) const { return lds32u(s, pos); }
+    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
+                                         uint32_t& b3) const { lds16u(s, pos, b0, b1, b2, b3); }
+};
+
+struct GlobalSrc {                       // fragment read in place from global memory
+    const uint8_t* g;                    // fragment start (any alignment)
+    __device__ __forceinline__ uint32_t ld32(uint32_t pos) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)a & 3u) << 3;
+        const uint32_t a0 = __ldg(w), a1 = sh ? __ldg(w + 1) : 0u;
+        return __funnelshift_r(a0, a1, sh);
+    }
+    // as ld32, but never touches a word that lies entirely at or beyond position `end` (the
+    // last fragment may end on the last mapped byte of the caller's buffer)
+    __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t end) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t r = (uint32_t)a & 3u;
+        const uint32_t a0 = __ldg(w), a1 = (r && pos + 4 - r < end) ? __ldg(w + 1) : 0u;
+        return __funnelshift_r(a0, a1, r << 3);
+    }
+    __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
+                                         uint32_t& b3) const {
+        const uintptr_t a = (uintptr_t)(g + pos);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)a & 3u) << 3;
+        const uint32_t a0 = __ldg(w), a1 = __ldg(w + 1), a2 = __ldg(w + 2), a3 = __ldg(w + 3);
+        const uint32_t a4 = sh ? __ldg(w + 4) : 0u;         // never touch a word without needed bytes
+        b0 = __funnelshift_r(a0, a1, sh);
+        b1 = __funnelshift_r(a1, a2, sh);
+        b2 = __funnelshift_r(a2, a3, sh);
+        b3 = __funnelshift_r(a3, a4, sh);
+    }
+};
+
+// FindMatchLength (snappy-internal.h:95-143) over an accessor, 128 bytes per round.
+template <class Src>
+__device__ __forceinline__ uint32_t src_match_len(const Src& src, uint32_t a, uint32_t b,
+                                                  uint32_t end, int lane) {
+    uint32_t n = 0;
+    for (;;) {
+        const uint32_t pb = b + n + (lane << 2);
+        uint32_t m = 0;
+        if (pb < end) {
+            const uint32_t x = src.ld32_upto(a + n + (lane << 2), end) ^ src.ld32_upto(pb, end);
+            m = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
+            m = min(m, end - pb);
+        }
+        const uint32_t bal = __ballot_sync(kFull, m < 4);
+        if (bal) {
+            const int first = __ffs(bal) - 1;
+            return n + (first << 2) + __shfl_sync(kFull, m, first);
+        }
+        n += 128;
+    }
+}
+
+// Serial scan (snappy.cc:587-608) over an accessor; see parse_serial.cuh.
+template <class Src>
+__device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table, int shift,
+                                                uint32_t ip_limit, uint32_t& ip, uint32_t& skip,
+                                                uint32_t& cand) {
+    uint32_t nxt = ip;
+    for (;;) {
+        ip = nxt;
+        const uint32_t step = skip >> 5;
+        skip += step;
+        nxt = ip + step;
+        if (nxt > ip_limit) return false;
+        const uint32_t w = src.ld32(ip);
+        const uint32_t h = hash32(w, shift);
+        cand = table[h];
+        table[h] = (uint16_t)ip;
+        if (src.ld32(cand) == w) return true;
+    }
+}
 
 // Write the pending inserts `I` of a window: table[h] = pos for every inserted lane, the highest
 // lane of a hash slot winning.  Without peers in the window no two lanes share a slot.
@@ -58,12 +140,11 @@ __device__ __forceinline__ void window_commit(uint16_t* table, uint32_t h, uint3
     }
 }
 
+template <class Src>
 struct WindowParser {
-    const uint8_t* s;
+    Src s;
     uint32_t len, ip_limit;
     uint16_t* table;
-    uint32_t* scr;          // peer-detector scratch, all 0xffffffff between windows
-    uint32_t scr_mask;
     int shift, lane;
     SeqWriter* out;
     uint32_t next_emit;
@@ -91,16 +172,13 @@ struct WindowParser {
             // ---- parallel set-up -----------------------------------------------------------
             const uint32_t wbase = win << 5;
             pos = wbase + lane;
-            uint32_t d0, d1, d2, d3;
-            lds16u(s, pos, d0, d1, d2, d3);
+            uint32_t d0 = 0, d1 = 0, d2 = 0, d3 = 0;
+            if (pos < ip_limit) s.ld16(pos, d0, d1, d2, d3);     // lanes past ip_limit never probe
             h = hash32(d0, shift);
             T = table[h];
-            uint32_t* slot = scr + (h & scr_mask);
-            atomicMin(slot, (uint32_t)lane);
             uint32_t c0, c1, c2, c3;
-            lds16u(s, T, c0, c1, c2, c3);
-            __syncwarp();
-            const bool peer = *slot != (uint32_t)lane;      // a lower lane has my hash (or aliases it)
+            s.ld16(T, c0, c1, c2, c3);
+            const bool peer = (__match_any_sync(kFull, h) & lt) != 0;   // a lower lane has my hash
             const bool hit = (c0 == d0);
             {
                 uint32_t x1 = c1 ^ d1, x2 = c2 ^ d2, x3 = c3 ^ d3, m = 12;
@@ -109,8 +187,6 @@ struct WindowParser {
                 if (x1) m = (uint32_t)(__ffs(x1) - 1) >> 3;
                 ml = m;
             }
-            __syncwarp();
-            *slot = kFull;                                  // reset the detector for the next window
             const uint32_t inval = ~__ballot_sync(kFull, pos < ip_limit);
             const uint32_t vpre_end = inval ? (uint32_t)__ffs(inval) - 1u : 32u;   // first lane past ip_limit
             const uint32_t VPRE = lanes_below(vpre_end);
@@ -160,8 +236,8 @@ struct WindowParser {
                     window_commit(table, h, pos, I, any_peer, lane);
                     if (vend < 32) {                         // 32 misses in a row: skip reached 64
                         uint32_t ip = wbase + vend, skip = 64, cand;
-                        if (!serial_scan(s, table, shift, ip_limit, ip, skip, cand)) return;
-                        const uint32_t matched = 4 + warp_match_len(s, cand + 4, ip + 4, len, lane);
+                        if (!src_serial_scan(s, table, shift, ip_limit, ip, skip, cand)) return;
+                        const uint32_t matched = 4 + src_match_len(s, cand + 4, ip + 4, len, lane);
                         out->push(ip - next_emit, matched, ip - cand, lane);
                         ip += matched;
                         next_emit = ip;
@@ -192,8 +268,8 @@ struct WindowParser {
                     const uint32_t cand = pk ? wbase + (31u - __clz(pk)) : __shfl_sync(kFull, T, fs);
                     const uint32_t p = wbase + fs;
                     I |= 1u << fs;
-                    if (lds32u(s, cand) != lds32u(s, p)) { sl = fs + 1; continue; }   // missed probe (:607)
-                    const uint32_t matched = 4 + warp_match_len(s, cand + 4, p + 4, len, lane);
+                    if (s.ld32(cand) != s.ld32(p)) { sl = fs + 1; continue; }   // missed probe (:607)
+                    const uint32_t matched = 4 + src_match_len(s, cand + 4, p + 4, len, lane);
                     out->push(p - next_emit, matched, p - cand, lane);
                     const uint32_t ip = p + matched;
                     next_emit = ip;
@@ -214,15 +290,15 @@ struct WindowParser {
     }
 };
 
-__device__ __forceinline__ void parse_fragment_window(const uint8_t* s, uint32_t len,
-                                                      uint16_t* table, uint32_t* scr,
-                                                      uint32_t scr_mask, int shift, SeqWriter& out,
+template <class Src>
+__device__ __forceinline__ void parse_fragment_window(const Src& s, uint32_t len,
+                                                      uint16_t* table, int shift, SeqWriter& out,
                                                       int lane) {
-    WindowParser wp;
+    WindowParser<Src> wp;
     wp.next_emit = 0;
     if (len >= kMargin) {                                   // snappy.cc:557
         wp.s = s; wp.len = len; wp.ip_limit = len - kMargin;   // :558
-        wp.table = table; wp.scr = scr; wp.scr_mask = scr_mask;
+        wp.table = table;
         wp.shift = shift; wp.lane = lane; wp.out = &out;
         wp.run();
     }
