@@ -309,18 +309,45 @@ def run_ours(args):
     out_n = torch.zeros(1, dtype=torch.int64, device=dev)
     torch.cuda.synchronize()
 
+    exchange = "none"
     if world > 1:
         from compression_accelerator_b200 import multi
-        sharder = multi.ArchiveGather(ctx, dev, cap)
+        # the exchange step: the library's own kernels over NVLink peer memory (csrc/peer.cuh); NCCL is
+        # only the rendezvous that passes the IPC handles around.  SNAPPY_B200_EXCHANGE=nccl selects
+        # the collective-library version (all_gather of sizes + send/recv) for comparison.
+        if os.environ.get("SNAPPY_B200_EXCHANGE", "peer") == "peer":
+            peer = multi.PeerArchive(ctx, dev, cap)
+            exchange = "peer"
+            dst2 = torch.empty(cap, dtype=torch.uint8, device=dev)
+            out_n2 = torch.zeros(1, dtype=torch.int64, device=dev)
+            bufs = [(dst, out_n), (dst2, out_n2)]
+            step_no = [0]
+        else:
+            sharder = multi.ArchiveGather(ctx, dev, cap)
+            exchange = "nccl"
+        torch.cuda.synchronize()
 
     mode_now = [args.mode]
 
     def step():
         """One pass of the hot path over this rank's batch (device-resident)."""
+        if exchange == "peer":
+            k = step_no[0]
+            peer.reuse(k - 2)                        # the buffer's last payload has left it
+            d, o = bufs[k & 1]
+            ctx.compress_device(src, d, o, mode=mode_now[0])
+            peer.gather(d, o, k)                     # behind the kernels just queued; no host round trip
+            step_no[0] = k + 1
+            return
         ctx.compress_device(src, dst, out_n, mode=mode_now[0])
         if world > 1:
             with torch.cuda.stream(stream):
                 sharder.exchange(dst, out_n)
+
+    def drain():
+        """Everything the steps queued is complete, on every rank, before the closing event."""
+        if exchange == "peer" and step_no[0]:
+            peer.wait_async(step_no[0] - 1)
 
     def timed(fn, k):
         if world > 1:
@@ -330,6 +357,7 @@ def run_ours(args):
         e0.record(stream)
         for _ in range(k):
             fn()
+        drain()
         e1.record(stream)
         torch.cuda.synchronize()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
@@ -343,7 +371,7 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    l0 = ctx.launches
+    l0 = ctx.launches + (peer.launches if exchange == "peer" else 0)
     parse_ms, gather_ms = [], []
 
     def step_probe():
@@ -353,7 +381,7 @@ def run_ours(args):
         gather_ms.append(ctx.stage_ms(1))
 
     ms = timed(step, args.steps)
-    launches = ctx.launches - l0
+    launches = ctx.launches + (peer.launches if exchange == "peer" else 0) - l0
     # a second, separately timed pass that syncs every step to read the per-kernel events
     for _ in range(args.steps):
         step_probe()
@@ -428,8 +456,11 @@ def run_ours(args):
                        "fragments_per_gpu": n // 65536, "compressed_bytes_per_gpu": comp_n,
                        "ratio_out_in": comp_n / n,
                        "l2": "input (1 GiB) and staging are larger than the 126 MB L2; no flush needed",
-                       "multi_gpu": "weak: 1 GiB per rank; NCCL all_gather of sizes + payload gather on rank 0"
-                       if world > 1 else "single GPU"},
+                       "multi_gpu": ("single GPU" if world == 1 else
+                                     "weak: 1 GiB per rank; sizes, offsets and payloads move to rank 0's archive by the "
+                                     "library's kernels over NVLink peer memory (CUDA IPC), two slots, step k's payload "
+                                     "moves while step k+1 is compressed" if exchange == "peer" else
+                                     "weak: 1 GiB per rank; NCCL all_gather of sizes + payload send/recv to rank 0")},
             "roofline": {"bound": "hbm", "kernel": "parse_pipe_kernel<true>" if args.mode == "exact" else "parse_fast_kernel",
                          "achieved": ach, "peak": peak,
                          "unit": "GB/s", "frac": ach / peak, "traffic": measured_traffic(args.mode), "peak_source": peak_src,
@@ -451,6 +482,13 @@ def run_ours(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        if exchange == "peer":                         # importers unmap before the root frees the archive
+            if rank != 0:
+                peer.close()
+            dist.barrier()
+            peer.close()
         dist.destroy_process_group()
 
 

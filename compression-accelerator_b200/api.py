@@ -78,6 +78,21 @@ SYMBOLS = {
     "snappy_b200_debug_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "snappy_b200_rocc_compress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
     "snappy_b200_rocc_uncompress": (C.c_ulong, [C.c_void_p, C.c_int, C.c_void_p]),
+    # multi-GPU exchange over peer memory (csrc/peer.cu)
+    "snappy_b200_peer_handle_bytes": (C.c_size_t, []),
+    "snappy_b200_peer_last_error": (C.c_char_p, []),
+    "snappy_b200_peer_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
+                                          C.POINTER(C.c_void_p)]),
+    "snappy_b200_peer_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "snappy_b200_peer_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_ulonglong]),
+    "snappy_b200_peer_reuse": (C.c_int, [C.c_void_p, C.c_ulonglong]),
+    "snappy_b200_peer_wait": (C.c_int, [C.c_void_p, C.c_ulonglong]),
+    "snappy_b200_peer_result": (C.c_int, [C.c_void_p, C.c_ulonglong, C.POINTER(C.c_ulonglong),
+                                          C.POINTER(C.c_ulonglong)]),
+    "snappy_b200_peer_archive": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "snappy_b200_peer_stream": (C.c_void_p, [C.c_void_p]),
+    "snappy_b200_peer_launch_count": (C.c_ulonglong, [C.c_void_p]),
+    "snappy_b200_peer_destroy": (None, [C.c_void_p]),
     # include/b200_rocc.h: the accelerator's top-level IO (ScratchpadTest.scala:23-51)
     "b200_rocc_new": (C.c_void_p, [C.c_size_t, C.c_int]),
     "b200_rocc_free": (None, [C.c_void_p]),

@@ -1,0 +1,122 @@
+// peer.cuh -- the multi-GPU exchange step over NVLink peer memory (include/snappy_b200.h,
+// snappy_b200_peer_*): one process per GPU, no collective library on the data path.
+//
+// What is exchanged (reference tests/snappy/snappy.cc:1061, the running output offset
+// is the only datum that crosses a fragment / stream boundary): every rank's payload size, and the
+// payloads themselves, which land back to back in an archive buffer on the root.  Each rank owns a
+// small MAILBOX in its HBM that every peer maps through CUDA IPC; the root also owns the archive
+// (two slots, steps alternate).  A step is three small kernels on the rank's exchange stream, behind
+// the compress kernels of that step:
+//   peer_publish_kernel  store (step, my size) into every rank's mailbox; wait for the sizes of the
+//                        ranks below me; my offset = their sum
+//   peer_copy_kernel     my payload -> root archive + offset, 16-byte stores through NVLink
+//   peer_finish_kernel   fence, then store "step done" into every rank's mailbox
+// Nothing here needs the host to know a size, so the next step's compress kernels are already
+// queued while the payload moves (the copy kernel is small enough to run beside the parser's CTAs).
+// Back-pressure: a rank starts step k only when every rank finished step k-2, so two mailbox /
+// archive slots suffice.  Every wait is bounded (about two seconds) and raises an error flag instead
+// of hanging the GPU.
+#pragma once
+#include "kernels.h"
+#include "snappy_device.cuh"
+#include "emit.cuh"
+
+namespace sb {
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t, uint32_t rank, uint32_t world,
+                                                                     unsigned long long step,
+                                                                     const unsigned long long* __restrict__ d_size,
+                                                                     unsigned long long* d_offset) {
+    __shared__ unsigned long long part[kPeerMaxWorld];
+    __shared__ int bad;
+    const uint32_t tid = threadIdx.x;
+    PeerMailbox* mine = t.box[rank];
+    if (tid == 0) bad = 0;
+    __syncthreads();
+    const long long t0 = clock64();
+    if (tid < world && step >= 2)                            // every rank is done with the slot I reuse
+        while (ld_acquire_sys(&mine->finished[tid]) + 1 < step)
+            if (clock64() - t0 > kPeerSpinCycles) { bad = 1; break; }
+    __syncthreads();
+    const unsigned long long size = *d_size;
+    const unsigned long long tag = (step + 1) << kPeerSizeBits;
+    if (tid < world) st_release_sys(&t.box[tid]->sizes[step & 1][rank], tag | size);
+    unsigned long long below = 0;
+    if (tid < rank) {
+        unsigned long long v;
+        while (((v = ld_acquire_sys(&mine->sizes[step & 1][tid])) >> kPeerSizeBits) != step + 1)
+            if (clock64() - t0 > 2 * kPeerSpinCycles) { bad = 1; break; }
+        below = v & ((1ull << kPeerSizeBits) - 1);
+    }
+    part[tid] = below;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long off = 0;
+        for (uint32_t r = 0; r < rank; ++r) off += part[r];
+        if (bad) { off = ~0ull; mine->error = 1; }
+        *d_offset = off;
+    }
+}
+
+__global__ void __launch_bounds__(256) peer_copy_kernel(const uint8_t* __restrict__ src,
+                                                        const unsigned long long* __restrict__ d_size,
+                                                        uint8_t* archive, unsigned long long archive_cap,
+                                                        const unsigned long long* __restrict__ d_offset,
+                                                        unsigned long long* d_error) {
+    const unsigned long long n = *d_size, off = *d_offset;
+    if (off == ~0ull) return;
+    if (off + n > archive_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) *d_error = 2; return; }
+    const unsigned long long tiles = (n + kPeerTile - 1) / kPeerTile;
+    for (unsigned long long k = blockIdx.x; k < tiles; k += gridDim.x) {
+        const unsigned long long lo = k * kPeerTile;
+        const uint32_t len = (uint32_t)(n - lo < kPeerTile ? n - lo : kPeerTile);
+        block_copy(archive + off + lo, src + lo, len, threadIdx.x, blockDim.x);
+    }
+}
+
+__global__ void __launch_bounds__(kPeerMaxWorld) peer_finish_kernel(PeerTable t, uint32_t rank, uint32_t world,
+                                                                    unsigned long long step) {
+    __threadfence_system();                                  // the copy kernel's stores, then the flag
+    if (threadIdx.x < world) st_release_sys(&t.box[threadIdx.x]->finished[rank], step + 1);
+}
+
+__global__ void __launch_bounds__(kPeerMaxWorld) peer_wait_kernel(PeerMailbox* mine, uint32_t world,
+                                                                  unsigned long long step) {
+    const long long t0 = clock64();
+    if (threadIdx.x < world)
+        while (ld_acquire_sys(&mine->finished[threadIdx.x]) < step + 1)
+            if (clock64() - t0 > 2 * kPeerSpinCycles) { mine->error = 3; break; }
+}
+
+
+cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, unsigned long long step,
+                             const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
+                             unsigned long long slot_bytes, unsigned long long* d_offset,
+                             unsigned long long* d_error, cudaStream_t st, cudaEvent_t copied,
+                             unsigned long long* launches) {
+    peer_publish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step, d_size, d_offset);
+    peer_copy_kernel<<<296, 256, 0, st>>>(payload, d_size, archive_slot, slot_bytes, d_offset, d_error);
+    cudaError_t e = cudaEventRecord(copied, st);
+    if (e != cudaSuccess) return e;
+    peer_finish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step);
+    if (launches) *launches += 3;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_peer_wait(PeerMailbox* mine, uint32_t world, unsigned long long step, cudaStream_t st,
+                             unsigned long long* launches) {
+    peer_wait_kernel<<<1, kPeerMaxWorld, 0, st>>>(mine, world, step);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace sb

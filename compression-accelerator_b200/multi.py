@@ -135,3 +135,86 @@ class ArchiveGather:
     def exchange(self, stream: torch.Tensor, out_n: torch.Tensor) -> int:
         self.total, self.offsets = self.ex.gather(stream, out_n, self.archive, base=0)
         return self.total
+
+
+class _DevicePtr:
+    """A raw device allocation of the library seen by torch (torch.as_tensor over
+    __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerArchive:
+    """The exchange step of bench.py's weak-scaling shape over NVLink peer memory: every rank
+    compresses its own stream, the streams land back to back in an archive slot on the root.  Sizes,
+    offsets and payload bytes move by the library's own kernels through CUDA-IPC peer pointers
+    (csrc/peer.cuh); the process group is used once, to pass the IPC handles around.  Nothing in a
+    step needs the host, so step k's payload moves while step k+1 is being compressed.
+
+        pa = PeerArchive(ctx, device, cap_per_rank)
+        for k in range(steps):
+            pa.reuse(k - 2)                      # buffer k % 2 is free again
+            ctx.compress_device(src, dst[k % 2], out_n[k % 2])
+            pa.gather(dst[k % 2], out_n[k % 2], k)
+        total, offsets = pa.wait(steps - 1)      # slot (steps - 1) % 2 on the root is complete
+    """
+
+    def __init__(self, ctx, device, cap_per_rank: int, group=None, root: int = 0):
+        import ctypes as C
+        from . import api
+        self._api, self._C = api, C
+        self.ctx, self.device, self.group, self.root = ctx, device, group, root
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.slot_bytes = cap_per_rank * self.world
+        L = api.lib()
+        hb = L.snappy_b200_peer_handle_bytes()
+        mine = C.create_string_buffer(hb)
+        h = C.c_void_p()
+        self._check(L.snappy_b200_peer_create(ctx._h, device.index, self.rank, self.world, root, self.slot_bytes,
+                                              mine, C.byref(h)))
+        self._h = h
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine.raw, group=group)
+        self._check(L.snappy_b200_peer_connect(self._h, b"".join(everyone)))
+        dist.barrier(group=group)                # every mailbox is mapped before anyone stores into one
+
+    def _check(self, status):
+        if status != 0:
+            raise self._api.SnappyB200Error(status, self._api.lib().snappy_b200_peer_last_error().decode())
+
+    def gather(self, payload: torch.Tensor, out_n: torch.Tensor, step: int):
+        """Asynchronous; ordered behind the work queued on the context's stream."""
+        self._check(self._api.lib().snappy_b200_peer_gather(self._h, payload.data_ptr(), out_n.data_ptr(), step))
+
+    def reuse(self, step: int):
+        if step >= 0:
+            self._check(self._api.lib().snappy_b200_peer_reuse(self._h, step))
+
+    def wait(self, step: int):
+        """Blocks until every rank's payload of `step` is in the root's slot; (total, offsets)."""
+        C, L = self._C, self._api.lib()
+        self._check(L.snappy_b200_peer_wait(self._h, step))
+        total = C.c_ulonglong()
+        offs = (C.c_ulonglong * self.world)()
+        self._check(L.snappy_b200_peer_result(self._h, step, C.byref(total), offs))
+        return total.value, list(offs)
+
+    def wait_async(self, step: int):
+        """Queue the wait only (the context's stream then follows the exchange stream)."""
+        self._check(self._api.lib().snappy_b200_peer_wait(self._h, step))
+
+    def archive(self, slot: int) -> torch.Tensor:
+        """The slot as a uint8 tensor (on non-root ranks: the root's memory as mapped here)."""
+        ptr = self._api.lib().snappy_b200_peer_archive(self._h, slot)
+        return torch.as_tensor(_DevicePtr(ptr, self.slot_bytes))
+
+    @property
+    def launches(self) -> int:
+        return self._api.lib().snappy_b200_peer_launch_count(self._h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._api.lib().snappy_b200_peer_destroy(self._h)
+            self._h = None

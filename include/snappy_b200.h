@@ -171,6 +171,39 @@ int snappy_b200_debug_stats(unsigned long long* out16, int reset);
 unsigned long snappy_b200_rocc_compress(char* source, int uncompressed_length, char* dest);
 unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, char* dest);
 
+/* ---- multi-GPU exchange over NVLink peer memory (one process per GPU).  The only
+ * datum that crosses a fragment or stream boundary is the running output offset
+ * (tests/snappy/snappy.cc:1061), so a step exchanges every rank's payload size and lands the
+ * payloads back to back in an archive on the root.  Mailboxes and the archive (two slots, steps
+ * alternate) live in device memory shared through CUDA IPC; sizes, offsets and payload bytes move by
+ * kernels of this library over peer pointers -- no host round trip, no collective library.
+ *   create   allocates this rank's side and writes snappy_b200_peer_handle_bytes() bytes of IPC
+ *            handles to handles_out; the caller exchanges them by any means (rank order, concatenated)
+ *   connect  maps the peers' mailboxes and the root's archive
+ *   gather   queues one step behind the work already on ctx's stream: payload d_payload[0, *d_size)
+ *            -> root archive slot (step & 1).  Steps are numbered 0, 1, 2, ... on every rank.
+ *   reuse    makes ctx's stream wait until step's payload has left its buffer (before overwriting it)
+ *   wait     queues a wait for every rank's step to be complete (then the slot may be read)
+ *   result   blocks the host on the last wait; total bytes in the slot and each rank's offset
+ * Every device-side wait is bounded (about 20 s) and reports through result() instead of hanging. */
+typedef struct snappy_b200_peer snappy_b200_peer;
+size_t snappy_b200_peer_handle_bytes(void);
+const char* snappy_b200_peer_last_error(void);
+snappy_b200_status snappy_b200_peer_create(snappy_b200_ctx* ctx, int device, int rank, int world, int root,
+                                           size_t archive_slot_bytes, void* handles_out,
+                                           snappy_b200_peer** out);
+snappy_b200_status snappy_b200_peer_connect(snappy_b200_peer* peer, const void* all_handles);
+snappy_b200_status snappy_b200_peer_gather(snappy_b200_peer* peer, const void* d_payload,
+                                           const unsigned long long* d_size, unsigned long long step);
+snappy_b200_status snappy_b200_peer_reuse(snappy_b200_peer* peer, unsigned long long step);
+snappy_b200_status snappy_b200_peer_wait(snappy_b200_peer* peer, unsigned long long step);
+snappy_b200_status snappy_b200_peer_result(snappy_b200_peer* peer, unsigned long long step,
+                                           unsigned long long* total, unsigned long long* offsets);
+void* snappy_b200_peer_archive(snappy_b200_peer* peer, int slot);   /* device pointer (mapped on non-root ranks) */
+void* snappy_b200_peer_stream(snappy_b200_peer* peer);              /* the exchange cudaStream_t */
+unsigned long long snappy_b200_peer_launch_count(snappy_b200_peer* peer);
+void snappy_b200_peer_destroy(snappy_b200_peer* peer);
+
 #ifdef __cplusplus
 }
 #endif
