@@ -84,10 +84,10 @@ SYMBOLS = {
     "snappy_b200_peer_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p,
                                           C.POINTER(C.c_void_p)]),
     "snappy_b200_peer_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
-    "snappy_b200_peer_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_ulonglong]),
+    "snappy_b200_peer_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_ulonglong, C.c_ulonglong]),
     "snappy_b200_peer_reuse": (C.c_int, [C.c_void_p, C.c_ulonglong]),
     "snappy_b200_peer_wait": (C.c_int, [C.c_void_p, C.c_ulonglong]),
-    "snappy_b200_peer_result": (C.c_int, [C.c_void_p, C.c_ulonglong, C.POINTER(C.c_ulonglong),
+    "snappy_b200_peer_result": (C.c_int, [C.c_void_p, C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong),
                                           C.POINTER(C.c_ulonglong)]),
     "snappy_b200_peer_archive": (C.c_void_p, [C.c_void_p, C.c_int]),
     "snappy_b200_peer_stream": (C.c_void_p, [C.c_void_p]),

@@ -21,6 +21,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "frame.cuh"
 #include "peer.cuh"
 #include <type_traits>
+#include <cstdlib>
 
 namespace sb {
 
@@ -397,6 +398,17 @@ cudaError_t kernels_init() {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCrcSmemBytes);
     if (e != cudaSuccess) return e;
+    // The exchange kernels run beside the parser's CTAs: ask for the parser's shared-memory carve-out
+    // (the maximum) so that placing them never calls for another split of an SM.  (Measured neutral on
+    // 2 GPUs; kept because a re-partition needs a drained SM.)
+    {
+        const void* beside[] = {(const void*)peer_publish_kernel, (const void*)peer_copy_kernel,
+                                (const void*)peer_finish_kernel, (const void*)peer_wait_kernel};
+        for (const void* f : beside) {
+            e = cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+            if (e != cudaSuccess) return e;
+        }
+    }
     static CrcOps ops;                                      // "append 2^k zero bytes" operators of CRC-32C
     crc_ops_build(ops);
     return cudaMemcpyToSymbol(g_crc_ops, &ops, sizeof(ops));

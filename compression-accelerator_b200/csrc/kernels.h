@@ -109,7 +109,6 @@ cudaError_t kernels_init();  // one-time function attributes (dynamic shared mem
 constexpr uint32_t kPeerMaxWorld = 64;
 constexpr uint64_t kPeerSizeBits = 40;                       // payload sizes < 1 TiB
 constexpr long long kPeerSpinCycles = 20000000000ll;         // ~10 s at 1.9 GHz
-constexpr uint32_t kPeerTile = 1u << 16;
 
 struct PeerMailbox {
     unsigned long long sizes[2][kPeerMaxWorld];              // (step + 1) << 40 | size, slot = step & 1
@@ -122,7 +121,7 @@ struct PeerTable {
 };
 
 cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, unsigned long long step,
-                             const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
+                             unsigned long long base, const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
                              unsigned long long slot_bytes, unsigned long long* d_offset,
                              unsigned long long* d_error, cudaStream_t st, cudaEvent_t copied,
                              unsigned long long* launches);

@@ -103,13 +103,14 @@ snappy_b200_status snappy_b200_peer_connect(snappy_b200_peer* p, const void* all
 }
 
 snappy_b200_status snappy_b200_peer_gather(snappy_b200_peer* p, const void* d_payload,
-                                           const unsigned long long* d_size, unsigned long long step) {
+                                           const unsigned long long* d_size, unsigned long long step,
+                                           unsigned long long base) {
     if (!p || !d_payload || !d_size) return pfail(SNAPPY_B200_INVALID_INPUT, "peer_gather: null argument");
     PCU(cudaSetDevice(p->device));
     cudaStream_t cs = (cudaStream_t)snappy_b200_stream(p->ctx);
     PCU(cudaEventRecord(p->ev_in, cs));                      // behind the compress kernels queued so far
     PCU(cudaStreamWaitEvent(p->xs, p->ev_in, 0));
-    PCU(sb::launch_peer_step(p->table, p->rank, p->world, step, (const uint8_t*)d_payload, d_size,
+    PCU(sb::launch_peer_step(p->table, p->rank, p->world, step, base, (const uint8_t*)d_payload, d_size,
                              p->archive + (step & 1) * p->slot_bytes, p->slot_bytes, p->d_offset + (step & 1),
                              &p->box->error, p->xs, p->ev_copied[step & 1], &p->launches));
     return SNAPPY_B200_OK;
@@ -133,14 +134,15 @@ snappy_b200_status snappy_b200_peer_wait(snappy_b200_peer* p, unsigned long long
 }
 
 snappy_b200_status snappy_b200_peer_result(snappy_b200_peer* p, unsigned long long step,
-                                           unsigned long long* total, unsigned long long* offsets) {
+                                           unsigned long long base, unsigned long long* total,
+                                           unsigned long long* offsets) {
     if (!p || !total) return pfail(SNAPPY_B200_INVALID_INPUT, "peer_result: null argument");
     PCU(cudaSetDevice(p->device));
     PCU(cudaEventSynchronize(p->ev_wait));
     const sb::PeerMailbox* m = (const sb::PeerMailbox*)p->h_box;
     if (m->error) return pfail(SNAPPY_B200_CUDA_ERROR, m->error == 2 ? "peer exchange: archive slot too small"
                                                                      : "peer exchange: a rank did not arrive in time");
-    unsigned long long run = 0;
+    unsigned long long run = base;
     for (uint32_t r = 0; r < p->world; ++r) {
         const unsigned long long v = m->sizes[step & 1][r];
         if ((v >> sb::kPeerSizeBits) != step + 1) return pfail(SNAPPY_B200_CUDA_ERROR, "peer exchange: stale size word");

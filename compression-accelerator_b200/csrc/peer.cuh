@@ -20,6 +20,7 @@
 #include "kernels.h"
 #include "snappy_device.cuh"
 #include "emit.cuh"
+#include <cstdlib>
 
 namespace sb {
 
@@ -33,7 +34,7 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 }
 
 __global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t, uint32_t rank, uint32_t world,
-                                                                     unsigned long long step,
+                                                                     unsigned long long step, unsigned long long base,
                                                                      const unsigned long long* __restrict__ d_size,
                                                                      unsigned long long* d_offset) {
     __shared__ unsigned long long part[kPeerMaxWorld];
@@ -60,26 +61,68 @@ __global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t
     part[tid] = below;
     __syncthreads();
     if (tid == 0) {
-        unsigned long long off = 0;
+        unsigned long long off = base;                       // bytes the root keeps in front (a stream header)
         for (uint32_t r = 0; r < rank; ++r) off += part[r];
         if (bad) { off = ~0ull; mine->error = 1; }
         *d_offset = off;
     }
 }
 
+// block_copy (emit.cuh) with four 16-byte chunks in flight per thread: the stores cross NVLink, the
+// loads come from local HBM, and a thread that waits for one load per store leaves the link idle.
+__device__ __forceinline__ void peer_tile_copy(uint8_t* __restrict__ d, const uint8_t* __restrict__ s,
+                                               uint32_t n, uint32_t tid, uint32_t nthreads) {
+    uint32_t head = (uint32_t)((16u - ((uintptr_t)d & 15u)) & 15u);
+    if (head > n) head = n;
+    if (tid < head) d[tid] = s[tid];
+    const uint32_t body = (n - head) >> 4;
+    if (body) {
+        uint4* d4 = reinterpret_cast<uint4*>(d + head);
+        const uint8_t* sb_ = s + head;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)sb_ & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)(uintptr_t)sb_ & 3u) << 3;
+        for (uint32_t j0 = tid; j0 < body; j0 += 4 * nthreads) {
+            uint32_t a[4][5];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t j = j0 + u * nthreads;
+                if (j < body) {
+                    const uint32_t* q = w + (j << 2);
+                    a[u][0] = __ldg(q); a[u][1] = __ldg(q + 1); a[u][2] = __ldg(q + 2); a[u][3] = __ldg(q + 3);
+                    a[u][4] = sh ? __ldg(q + 4) : 0u;  // never read past the source when aligned
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t j = j0 + u * nthreads;
+                if (j < body) {
+                    uint4 v;
+                    v.x = __funnelshift_r(a[u][0], a[u][1], sh);
+                    v.y = __funnelshift_r(a[u][1], a[u][2], sh);
+                    v.z = __funnelshift_r(a[u][2], a[u][3], sh);
+                    v.w = __funnelshift_r(a[u][3], a[u][4], sh);
+                    d4[j] = v;
+                }
+            }
+        }
+    }
+    const uint32_t done = head + (body << 4);
+    if (done + tid < n) d[done + tid] = s[done + tid];
+}
+
 __global__ void __launch_bounds__(256) peer_copy_kernel(const uint8_t* __restrict__ src,
                                                         const unsigned long long* __restrict__ d_size,
                                                         uint8_t* archive, unsigned long long archive_cap,
                                                         const unsigned long long* __restrict__ d_offset,
-                                                        unsigned long long* d_error) {
+                                                        unsigned long long* d_error, uint32_t tile) {
     const unsigned long long n = *d_size, off = *d_offset;
     if (off == ~0ull) return;
     if (off + n > archive_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) *d_error = 2; return; }
-    const unsigned long long tiles = (n + kPeerTile - 1) / kPeerTile;
+    const unsigned long long tiles = (n + tile - 1) / tile;
     for (unsigned long long k = blockIdx.x; k < tiles; k += gridDim.x) {
-        const unsigned long long lo = k * kPeerTile;
-        const uint32_t len = (uint32_t)(n - lo < kPeerTile ? n - lo : kPeerTile);
-        block_copy(archive + off + lo, src + lo, len, threadIdx.x, blockDim.x);
+        const unsigned long long lo = k * tile;
+        const uint32_t len = (uint32_t)(n - lo < tile ? n - lo : tile);
+        peer_tile_copy(archive + off + lo, src + lo, len, threadIdx.x, blockDim.x);
     }
 }
 
@@ -99,12 +142,17 @@ __global__ void __launch_bounds__(kPeerMaxWorld) peer_wait_kernel(PeerMailbox* m
 
 
 cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, unsigned long long step,
-                             const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
+                             unsigned long long base, const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
                              unsigned long long slot_bytes, unsigned long long* d_offset,
                              unsigned long long* d_error, cudaStream_t st, cudaEvent_t copied,
                              unsigned long long* launches) {
-    peer_publish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step, d_size, d_offset);
-    peer_copy_kernel<<<296, 256, 0, st>>>(payload, d_size, archive_slot, slot_bytes, d_offset, d_error);
+    peer_publish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step, base, d_size, d_offset);
+    // Few CTAs on purpose: 32 reach ~500 GB/s over NVLink when alone, and remote stores back up the
+    // load/store path of the SM they run on, which slows the parser's CTAs sharing it (2 GPUs, ms per
+    // step: 296 CTAs 33.70, 32 CTAs 33.36, 12 CTAs 33.61).  SNAPPY_B200_PEER_CTAS / _TILE_KB for A/B.
+    static const uint32_t ctas = [] { const char* e = getenv("SNAPPY_B200_PEER_CTAS"); return e ? (uint32_t)atoi(e) : 32u; }();
+    static const uint32_t tile = [] { const char* e = getenv("SNAPPY_B200_PEER_TILE_KB"); return (e ? (uint32_t)atoi(e) : 256u) << 10; }();
+    peer_copy_kernel<<<ctas, 256, 0, st>>>(payload, d_size, archive_slot, slot_bytes, d_offset, d_error, tile);
     cudaError_t e = cudaEventRecord(copied, st);
     if (e != cudaSuccess) return e;
     peer_finish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step);

@@ -184,21 +184,22 @@ class PeerArchive:
         if status != 0:
             raise self._api.SnappyB200Error(status, self._api.lib().snappy_b200_peer_last_error().decode())
 
-    def gather(self, payload: torch.Tensor, out_n: torch.Tensor, step: int):
-        """Asynchronous; ordered behind the work queued on the context's stream."""
-        self._check(self._api.lib().snappy_b200_peer_gather(self._h, payload.data_ptr(), out_n.data_ptr(), step))
+    def gather(self, payload: torch.Tensor, out_n: torch.Tensor, step: int, base: int = 0):
+        """Asynchronous; ordered behind the work queued on the context's stream.  base = bytes the root
+        keeps at the front of the slot (the varint preamble of a stream sharded over the ranks)."""
+        self._check(self._api.lib().snappy_b200_peer_gather(self._h, payload.data_ptr(), out_n.data_ptr(), step, base))
 
     def reuse(self, step: int):
         if step >= 0:
             self._check(self._api.lib().snappy_b200_peer_reuse(self._h, step))
 
-    def wait(self, step: int):
+    def wait(self, step: int, base: int = 0):
         """Blocks until every rank's payload of `step` is in the root's slot; (total, offsets)."""
         C, L = self._C, self._api.lib()
         self._check(L.snappy_b200_peer_wait(self._h, step))
         total = C.c_ulonglong()
         offs = (C.c_ulonglong * self.world)()
-        self._check(L.snappy_b200_peer_result(self._h, step, C.byref(total), offs))
+        self._check(L.snappy_b200_peer_result(self._h, step, base, C.byref(total), offs))
         return total.value, list(offs)
 
     def wait_async(self, step: int):
@@ -218,3 +219,49 @@ class PeerArchive:
         if getattr(self, "_h", None):
             self._api.lib().snappy_b200_peer_destroy(self._h)
             self._h = None
+
+
+class PeerShardedStream:
+    """ONE Snappy stream of n_total bytes (< 2^32) compressed by all ranks, assembled on the root over
+    NVLink peer memory: rank r compresses fragments [F*r/R, F*(r+1)/R) header-less, its payload lands
+    behind the varint preamble and the payloads of the ranks below (PeerArchive with base = preamble).
+    Byte-identical to the single-GPU stream (tests/test_multi_gpu.py)."""
+
+    def __init__(self, ctx, n_total: int, device, group=None, root: int = 0):
+        if n_total >= 1 << 32:
+            raise ValueError("a Snappy stream holds < 2^32 bytes; use an archive of streams")
+        from . import api
+        self.ctx, self.n_total, self.device, self.root = ctx, n_total, device, root
+        world = dist.get_world_size(group)
+        self.lo, self.hi = fragment_range(n_total, dist.get_rank(group), world)
+        self.header = varint32(n_total)
+        cap = api.max_compressed_length(n_total) + 64
+        self.pa = PeerArchive(ctx, device, -(-cap // world), group, root)
+        shard_cap = api.max_compressed_length(self.hi - self.lo)
+        self._bufs = [(torch.empty(shard_cap, dtype=torch.uint8, device=device),
+                       torch.zeros(1, dtype=torch.int64, device=device)) for _ in range(2)]
+        self.step = 0
+
+    def submit(self, src_shard: torch.Tensor) -> int:
+        """Queue this rank's part of one stream (src_shard = bytes [lo, hi) of the input); returns the step.
+        Two streams may be in flight: finish(k) before submit of step k + 2 (its slot is reused)."""
+        k = self.step
+        self.pa.reuse(k - 2)
+        d, o = self._bufs[k & 1]
+        self.ctx.compress_device(src_shard, d, o, header=False)
+        self.pa.gather(d, o, k, base=len(self.header))
+        self.step = k + 1
+        return k
+
+    def finish(self, step: int):
+        """Blocks until the stream of `step` is complete on the root; returns (length, tensor or None)."""
+        total, _ = self.pa.wait(step, base=len(self.header))
+        if self.pa.rank != self.root:
+            return total, None
+        slot = self.pa.archive(step & 1)
+        slot[:len(self.header)].copy_(torch.frombuffer(bytearray(self.header), dtype=torch.uint8))
+        torch.cuda.synchronize(self.device)
+        return total, slot[:total]
+
+    def close(self):
+        self.pa.close()

@@ -181,7 +181,9 @@ unsigned long snappy_b200_rocc_uncompress(char* source, int compressed_length, c
  *            handles to handles_out; the caller exchanges them by any means (rank order, concatenated)
  *   connect  maps the peers' mailboxes and the root's archive
  *   gather   queues one step behind the work already on ctx's stream: payload d_payload[0, *d_size)
- *            -> root archive slot (step & 1).  Steps are numbered 0, 1, 2, ... on every rank.
+ *            -> root archive slot (step & 1), behind `base` bytes the root keeps for itself (the
+ *            varint preamble when the ranks hold runs of fragments of ONE stream, else 0) and the
+ *            payloads of the ranks below.  Steps are numbered 0, 1, 2, ... on every rank.
  *   reuse    makes ctx's stream wait until step's payload has left its buffer (before overwriting it)
  *   wait     queues a wait for every rank's step to be complete (then the slot may be read)
  *   result   blocks the host on the last wait; total bytes in the slot and each rank's offset
@@ -194,11 +196,13 @@ snappy_b200_status snappy_b200_peer_create(snappy_b200_ctx* ctx, int device, int
                                            snappy_b200_peer** out);
 snappy_b200_status snappy_b200_peer_connect(snappy_b200_peer* peer, const void* all_handles);
 snappy_b200_status snappy_b200_peer_gather(snappy_b200_peer* peer, const void* d_payload,
-                                           const unsigned long long* d_size, unsigned long long step);
+                                           const unsigned long long* d_size, unsigned long long step,
+                                           unsigned long long base);
 snappy_b200_status snappy_b200_peer_reuse(snappy_b200_peer* peer, unsigned long long step);
 snappy_b200_status snappy_b200_peer_wait(snappy_b200_peer* peer, unsigned long long step);
 snappy_b200_status snappy_b200_peer_result(snappy_b200_peer* peer, unsigned long long step,
-                                           unsigned long long* total, unsigned long long* offsets);
+                                           unsigned long long base, unsigned long long* total,
+                                           unsigned long long* offsets);
 void* snappy_b200_peer_archive(snappy_b200_peer* peer, int slot);   /* device pointer (mapped on non-root ranks) */
 void* snappy_b200_peer_stream(snappy_b200_peer* peer);              /* the exchange cudaStream_t */
 unsigned long long snappy_b200_peer_launch_count(snappy_b200_peer* peer);

@@ -142,3 +142,64 @@ def test_peer_archive_over_nvlink():
     res = [q.get(timeout=5) for _ in range(world)]
     assert all(ok for _, ok, _ in res), res
     assert len({t for _, _, t in res}) == 1          # every rank saw the same total
+
+
+def _peer_stream_worker(rank, world, port, n_total, q):
+    for p in (HERE, ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import __graft_entry__ as g
+    import oracle_lib
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        pkg = g.load_package()
+        from compression_accelerator_b200 import multi
+        ctx = pkg.Context(rank)
+        host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n_total)
+        sh = multi.PeerShardedStream(ctx, n_total, dev)
+        shard = torch.from_numpy(host[sh.lo:sh.hi].copy()).to(dev)
+        torch.cuda.synchronize()
+        want = oracle_lib.checker().compress(host.tobytes()) if rank == 0 else None
+        ok = True
+
+        def check(k):
+            total, x = sh.finish(k)
+            return rank != 0 or (total == len(want) and bytes(x.cpu().numpy()) == want)
+
+        sh.submit(shard)                                  # the same stream three times, two in flight
+        sh.submit(shard)
+        ok = check(0) and ok
+        sh.submit(shard)
+        ok = check(1) and ok
+        ok = check(2) and ok
+        if rank == 0:
+            q.put(ok)
+        dist.barrier()
+        if rank != 0:
+            sh.close()
+        dist.barrier()
+        sh.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_total", [65536 * 37 + 4321, 1 << 26])
+def test_sharded_stream_over_peer_memory(n_total):
+    """One stream, fragments sharded over the GPUs, assembled over NVLink peer memory: byte-identical
+    to the oracle's one-shot stream."""
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_stream_worker, args=(r, world, port, n_total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    assert q.get(timeout=5)
