@@ -315,8 +315,13 @@ def run_ours(args):
         # the exchange step: the library's own kernels over NVLink peer memory (csrc/peer.cuh); NCCL is
         # only the rendezvous that passes the IPC handles around.  SNAPPY_B200_EXCHANGE=nccl selects
         # the collective-library version (all_gather of sizes + send/recv) for comparison.
+        peer = None
         if os.environ.get("SNAPPY_B200_EXCHANGE", "peer") == "peer":
-            peer = multi.PeerArchive(ctx, dev, cap)
+            try:
+                peer = multi.PeerArchive(ctx, dev, cap)   # raises on every rank or on none
+            except Exception as e:                        # no CUDA IPC between these GPUs: NCCL exchange
+                log("peer-memory exchange unavailable (%r); using the NCCL exchange" % (e,))
+        if peer is not None:
             exchange = "peer"
             dst2 = torch.empty(cap, dtype=torch.uint8, device=dev)
             out_n2 = torch.zeros(1, dtype=torch.int64, device=dev)

@@ -172,13 +172,25 @@ class PeerArchive:
         hb = L.snappy_b200_peer_handle_bytes()
         mine = C.create_string_buffer(hb)
         h = C.c_void_p()
-        self._check(L.snappy_b200_peer_create(ctx._h, device.index, self.rank, self.world, root, self.slot_bytes,
-                                              mine, C.byref(h)))
+        self._h = None
+        # every rank learns whether every rank got through a stage, so a failure raises everywhere
+        # instead of leaving the others inside a collective
+        st = L.snappy_b200_peer_create(ctx._h, device.index, self.rank, self.world, root, self.slot_bytes,
+                                       mine, C.byref(h))
+        self._agree(st, "peer_create")
         self._h = h
         everyone = [None] * self.world
         dist.all_gather_object(everyone, mine.raw, group=group)
-        self._check(L.snappy_b200_peer_connect(self._h, b"".join(everyone)))
-        dist.barrier(group=group)                # every mailbox is mapped before anyone stores into one
+        st = L.snappy_b200_peer_connect(self._h, b"".join(everyone))
+        self._agree(st, "peer_connect")          # also: every mailbox is mapped before anyone stores into one
+
+    def _agree(self, status, what):
+        text = self._api.lib().snappy_b200_peer_last_error().decode() if status else ""
+        flag = torch.tensor([1 if status == 0 else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            self.close()
+            raise self._api.SnappyB200Error(status or 3, "%s failed on some rank%s" % (what, ": " + text if text else ""))
 
     def _check(self, status):
         if status != 0:
