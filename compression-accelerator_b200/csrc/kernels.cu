@@ -58,17 +58,15 @@ __device__ __forceinline__ void stage_fragment(const uint8_t* __restrict__ src, 
     if (bulk) mbar_wait(bar, 0);
 }
 
-// One warp per job; a CTA holds kw warps (jobs kw*blockIdx.x ...), each with its own slice of shared
-// memory.  More than one job per CTA only spreads the per-CTA shared-memory reservation over several
-// page-sized jobs (18 instead of 17 4 KiB pages per SM); the warps never meet.
-constexpr uint32_t kMaxJobWarps = 4;
+// One warp (one CTA) per job.  Packing several page-sized jobs into one CTA to spread the per-CTA
+// shared-memory reservation (18 instead of 17 4 KiB pages per SM) was measured and lost: a CTA's
+// resources return only when its slowest job ends, and the kernel compiled for more than one warp per
+// CTA ran 12 % slower per page (85 -> 75-77 GB/s on 4 KiB text pages).
 template <bool kWindow>
-__global__ void __launch_bounds__(32 * kMaxJobWarps, 10) parse_kernel(JobParams p, uint32_t slice) {   // <= 48 registers
-    extern __shared__ __align__(128) uint8_t smem_all[];
-    const int lane = threadIdx.x & 31;
-    const uint32_t job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (job >= p.n_jobs) return;
-    uint8_t* smem = smem_all + (threadIdx.x >> 5) * slice;
+__global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x;
+    const uint32_t job = blockIdx.x;
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     uint16_t* table = reinterpret_cast<uint16_t*>(smem + kSmemTableOff);
     const uint32_t len = job_len_of(p, job);
@@ -80,26 +78,6 @@ __global__ void __launch_bounds__(32 * kMaxJobWarps, 10) parse_kernel(JobParams 
     if (kWindow) parse_fragment_window(SmemSrc{s_in}, len, table, shift, out, lane);
     else parse_fragment_serial(s_in, len, table, shift, out, lane);
     if (lane == 0) p.nseq[job] = out.n;
-}
-
-// Warps per CTA that put the most single-warp jobs on an SM (228 KB shared memory with 1 KB
-// reserved per CTA, 32 CTAs, and the register file: 48 registers per thread, see __launch_bounds__).
-inline uint32_t job_warps(uint32_t slice) {
-    uint32_t best = 1, best_jobs = 0;
-    for (uint32_t w = 1; w <= kMaxJobWarps; ++w) {
-        if ((size_t)w * slice > 227u * 1024u) break;
-        uint32_t ctas = 233472u / ((w * slice + 1024u + 255u) & ~255u);   // allocation granularity
-        if (ctas > 32u) ctas = 32u;
-        if (ctas * w > 40u) ctas = 40u / w;                  // 65536 registers / (32 lanes * 48)
-        if (ctas * w > best_jobs) { best_jobs = ctas * w; best = w; }
-    }
-    return best;
-}
-template <bool kWindow>
-inline void launch_job_warps(const JobParams& p, cudaStream_t st) {
-    const uint32_t slice = (parse_smem_bytes(p.job_len) + 15u) & ~15u;
-    const uint32_t w = job_warps(slice);
-    parse_kernel<kWindow><<<(p.n_jobs + w - 1) / w, 32 * w, (size_t)w * slice, st>>>(p, slice);
 }
 
 // ---- pipelined parser: one resolver warp + P producer warps per fragment ----------------------
@@ -379,10 +357,10 @@ cudaError_t read_stats(unsigned long long* out16, bool reset) {
 
 cudaError_t kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         227 * 1024);
+                                         (int)parse_smem_bytes(kBlock));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             227 * 1024);
+                             (int)parse_smem_bytes(kBlock));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(parse_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)pipe_smem_bytes<false>(kBlock));
@@ -420,12 +398,12 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
     if (mode == 1) {
         const uint32_t K = fast_evaluators(p.job_len);      // 14 -> the 16-warp CTA (12 of them evaluate)
         parse_fast_kernel<<<p.n_jobs, 32 * (2 + K), fast_layout(p.job_len).total, st>>>(p);
-    } else if (mode == 2) launch_job_warps<false>(p, st);
+    } else if (mode == 2) parse_kernel<false><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     else if (mode == 0 && p.job_len > SB_PIPE_MIN_LEN)   // small jobs fit many per SM: the single-warp parser wins
         parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
     else if (mode == 4)
         parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);
-    else launch_job_warps<true>(p, st);
+    else parse_kernel<true><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -102,7 +102,8 @@ def test_batch_pages_exact(ctx, oracle):
         assert bytes(out[i * ostride:i * ostride + 2]) == b"\x80\x20"
 
 
-@pytest.mark.parametrize("length", [1, 14, 15, 100, 255, 256, 1000, 5000, 16384, 50000, 65536])
+@pytest.mark.parametrize("length", [1, 14, 15, 100, 255, 256, 1000, 2048, 4096, 5000, 8192, 8193, 12000, 16384, 50000,
+                                    65536])
 def test_batch_size_sweep(ctx, oracle, length):
     text = corpus.fixture("alice29.txt")
     count = 16
@@ -112,6 +113,18 @@ def test_batch_size_sweep(ctx, oracle, length):
     for i in range(count):
         want = oracle.compress(bytes(buf[i * stride:i * stride + length]))
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
+
+
+@pytest.mark.parametrize("count", [1, 2, 5, 7])
+def test_batch_few_pages(ctx, oracle, count):
+    """Page jobs share a CTA (several warps, one job each): counts that leave warps of the last CTA idle."""
+    text = corpus.fixture("all-mtg-cards.txt")
+    for length in (1024, 4096):
+        buf = np.frombuffer(text[1000:1000 + length * count], dtype=np.uint8).copy()
+        out, ostride, sizes = ctx.compress_batch(buf, length, length, count)
+        for i in range(count):
+            want = oracle.compress(bytes(buf[i * length:(i + 1) * length]))
+            assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, (length, i)
 
 
 def test_fragment_range_entry(ctx, oracle):
