@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(128) size_kernel(JobParams p) {
     const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
     const uint32_t n = p.nseq[job];
     uint32_t sum = 0;
+#pragma unroll 4                          // four loads in flight per lane: the walk is latency-bound
     for (uint32_t i = lane; i < n; i += 32) sum += seq_encoded_size(q[i]);
     for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
     if (lane == 0) p.sizes[job] = sum + (p.with_header ? varint32_len(job_len_of(p, job)) : 0);
@@ -202,6 +203,11 @@ __device__ __forceinline__ void sparse_summary(const uint32_t* __restrict__ q, u
     bytes = __reduce_add_sync(kFull, sum);
 }
 
+// The size pass leaves its eight segment summaries behind the job's slots (the job's region of
+// `seqs` is twice as large as the slot list), so the emit pass does not walk the slots a third time.
+__device__ __forceinline__ bool sparse_keeps_summaries(uint32_t job_len) { return job_len >= 64u; }
+__device__ __forceinline__ uint32_t sparse_summary_at(uint32_t job_len) { return ((job_len + 31u) >> 5) << 3; }
+
 struct SparseChain {                     // shared: summaries in, carry-ins out
     uint32_t first_pos[kSparseWarps], last_end[kSparseWarps], bytes[kSparseWarps];
     uint32_t end_in[kSparseWarps + 1], out_in[kSparseWarps + 1];
@@ -222,12 +228,18 @@ __global__ void __launch_bounds__(kEmitThreads) size_sparse_kernel(JobParams p) 
     __shared__ SparseChain c;
     const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t len = job_len_of(p, job);
-    const uint32_t* q = reinterpret_cast<const uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
+    uint32_t* q = reinterpret_cast<uint32_t*>(p.seqs + (uint64_t)job * seq_stride(p.job_len));
     const uint32_t n = sparse_slots(len);
     uint32_t lo, hi, fp, le, by;
     sparse_segment(n, wid, lo, hi);
     sparse_summary(q, n, lo, hi, lane, fp, le, by);
-    if (lane == 0) { c.first_pos[wid] = fp; c.last_end[wid] = le; c.bytes[wid] = by; }
+    if (lane == 0) {
+        c.first_pos[wid] = fp; c.last_end[wid] = le; c.bytes[wid] = by;
+        if (sparse_keeps_summaries(p.job_len)) {
+            uint32_t* keep = q + sparse_summary_at(p.job_len) + 3 * wid;
+            keep[0] = fp; keep[1] = le; keep[2] = by;
+        }
+    }
     __syncthreads();
     if (tid == 0) {
         sparse_chain(c, p.with_header ? varint32_len(len) : 0u);
@@ -256,7 +268,12 @@ __global__ void __launch_bounds__(kEmitThreads) emit_sparse_kernel(JobParams p) 
     }
     uint32_t lo, hi, fp, le, by;
     sparse_segment(n, wid, lo, hi);
-    sparse_summary(q, n, lo, hi, lane, fp, le, by);
+    if (sparse_keeps_summaries(p.job_len)) {                 // left by size_sparse_kernel
+        const uint32_t* keep = q + sparse_summary_at(p.job_len) + 3 * wid;
+        fp = __ldg(keep); le = __ldg(keep + 1); by = __ldg(keep + 2);
+    } else {
+        sparse_summary(q, n, lo, hi, lane, fp, le, by);
+    }
     if (lane == 0) { c.first_pos[wid] = fp; c.last_end[wid] = le; c.bytes[wid] = by; }
     __syncthreads();
     if (tid == 0) sparse_chain(c, hdr);
