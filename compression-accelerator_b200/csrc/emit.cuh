@@ -1,5 +1,5 @@
 // emit.cuh -- from sequence lists to Snappy elements.
-//   size_kernel  one warp per job: encoded bytes of the job (EmitLiteral + EmitCopy sizes,
+//   size_kernel / size_block_kernel  one warp (page-sized jobs) or one CTA per job: encoded bytes of the job (EmitLiteral + EmitCopy sizes,
 //                tests/snappy/snappy.cc:337-431) [+ varint header in batch mode].
 //   emit_kernel  one CTA per job: block scan of per-sequence input/output lengths, then every
 //                thread encodes its own sequence at its final output position; long literals
@@ -22,17 +22,36 @@ __device__ __forceinline__ uint32_t seq_encoded_size(seq_t q) {
     return n;
 }
 
-__global__ void __launch_bounds__(128) size_kernel(JobParams p) {
+__global__ void __launch_bounds__(128) size_kernel(JobParams p) {            // page-sized jobs: one warp each
     const int lane = threadIdx.x & 31;
     const uint32_t job = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (job >= p.n_jobs) return;
     const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
     const uint32_t n = p.nseq[job];
     uint32_t sum = 0;
-#pragma unroll 4                          // four loads in flight per lane: the walk is latency-bound
     for (uint32_t i = lane; i < n; i += 32) sum += seq_encoded_size(q[i]);
     for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
     if (lane == 0) p.sizes[job] = sum + (p.with_header ? varint32_len(job_len_of(p, job)) : 0);
+}
+
+constexpr int kSizeThreads = 256;
+__global__ void __launch_bounds__(kSizeThreads) size_block_kernel(JobParams p) {
+    // one CTA per job: a lone warp walking a fragment's ~7 K sequences is a chain of ~230 dependent
+    // loads (130 us for any number of fragments up to a full wave)
+    __shared__ uint32_t part[kSizeThreads / 32];
+    const uint32_t tid = threadIdx.x, job = blockIdx.x;
+    const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+    const uint32_t n = p.nseq[job];
+    uint32_t sum = 0;
+    for (uint32_t i = tid; i < n; i += kSizeThreads) sum += seq_encoded_size(q[i]);
+    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
+    if ((tid & 31) == 0) part[tid >> 5] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t total = 0;
+        for (int w = 0; w < kSizeThreads / 32; ++w) total += part[w];
+        p.sizes[job] = total + (p.with_header ? varint32_len(job_len_of(p, job)) : 0);
+    }
 }
 
 // Cooperative copy of n bytes global -> global, both arbitrarily aligned: destination-aligned

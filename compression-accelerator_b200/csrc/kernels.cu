@@ -411,6 +411,7 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
     if (p.sparse) size_sparse_kernel<<<p.n_jobs, kEmitThreads, 0, st>>>(p);
+    else if (p.job_len > 8192) size_block_kernel<<<p.n_jobs, kSizeThreads, 0, st>>>(p);
     else size_kernel<<<(p.n_jobs + 3) / 4, 128, 0, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
