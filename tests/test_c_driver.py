@@ -41,3 +41,47 @@ def test_c_driver_thistle_known_answer(driver):
     assert lines[0] == "compress: 130 -> 112 bytes"
     assert lines[1].replace("stream:", "").replace(" ", "") == THISTLE_STREAM
     assert lines[2] == "uncompress: result 0, identical"
+
+
+@pytest.fixture(scope="module")
+def swcompress(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("swcompress") / "swcompress")
+    subprocess.run(["g++", "-std=c++11", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(HERE, "c_driver", "swcompress.cc"), "-L", LIBDIR, "-lsnappy_b200",
+                    "-Wl,-rpath," + LIBDIR, "-o", exe], check=True)
+    return exe
+
+
+def test_cpp_host_program_builds_and_has_no_cpu_path(swcompress):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present: covered by the gpu test")
+    r = subprocess.run([swcompress], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", [None, "fox-in-socks.txt", "all-mtg-cards.txt", "randomASCII.txt"])
+def test_cpp_host_program_matches_reference_snappy(swcompress, tmp_path, name):
+    """snappy::Compress call shape (tests/swcompression.cc:45) with the namespace switched: size and
+    FNV-1a of the stream equal the reference Snappy's (golden manifest), and the round trip holds."""
+    import corpus
+    args = [swcompress]
+    if name is None:
+        want = "130 112 %08x ok" % _fnv1a32(bytes.fromhex(THISTLE_STREAM))
+    else:
+        path = tmp_path / name
+        path.write_bytes(corpus.fixture(name))
+        args.append(str(path))
+        m = corpus.manifest()["files"][name]
+        want = "%d %d %s ok" % (m["n"], m["compressed_n"], m["fnv1a32"])
+    r = subprocess.run(args, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.strip() == want
+
+
+def _fnv1a32(data: bytes) -> int:
+    h = 2166136261
+    for b in data:
+        h = ((h ^ b) * 16777619) & 0xFFFFFFFF
+    return h
