@@ -52,6 +52,20 @@ def test_no_cpu_fallback(pkg):
     assert pkg.rocc_compress(b"abc", 3, buf) == 0          # RoCC mirror: 0 = failure
 
 
+def test_peer_exchange_argument_checks(pkg):
+    """The peer-memory exchange entries reject bad arguments before touching a device."""
+    L = pkg.lib()
+    assert L.snappy_b200_peer_handle_bytes() == 128          # two cudaIpcMemHandle_t
+    h = C.c_void_p()
+    buf = C.create_string_buffer(128)
+    assert L.snappy_b200_peer_create(None, 0, 0, 2, 0, 1 << 20, buf, C.byref(h)) == 1     # null context
+    assert b"peer_create" in L.snappy_b200_peer_last_error()
+    assert L.snappy_b200_peer_connect(None, buf) == 1
+    assert L.snappy_b200_peer_gather(None, None, None, 0, 0) == 1
+    assert L.snappy_b200_peer_archive(None, 0) is None
+    L.snappy_b200_peer_destroy(None)                          # no-op
+
+
 def test_product_does_not_reference_oracle():
     for dp, _, fns in os.walk(os.path.join(ROOT, "compression-accelerator_b200")):
         for fn in fns:
