@@ -51,12 +51,15 @@ struct DevBuf {
 // Parse streams of the chunked host entry.  A stream starts its next chunk only when ALL fragments of
 // its current one are done, so with S streams about S-1 chunks' worth of fragments are in flight: it
 // takes 8 x 16 MiB (2048 fragments) to keep the 888 resident slots of the exact parser full.
-constexpr int kParseStreams = 8;
+constexpr int kParseStreams = 32;
+constexpr int kPipeParseStreams = 8;
 inline int pipe_streams() {
-    static const int n = [] { const char* e = getenv("SNAPPY_B200_PARSE_STREAMS"); int v = e ? atoi(e) : kParseStreams;
+    static const int n = [] { const char* e = getenv("SNAPPY_B200_PARSE_STREAMS"); int v = e ? atoi(e) : kPipeParseStreams;
                               return v < 1 ? 1 : v > kParseStreams ? kParseStreams : v; }();
     return n;
 }
+
+constexpr size_t kMaxChunks = 1024;
 
 struct snappy_b200_ctx {
     int device = 0;
@@ -64,6 +67,8 @@ struct snappy_b200_ctx {
     DevBuf seqs, nseq, sizes, offsets, d_in, d_out;
     DevBuf crcs, frame_ix, frame_res;          // framing: per-chunk CRCs, chunk index, walk result + flag
     DevBuf raw_ix;                             // segment / block index of one large raw stream (decode_par.cuh)
+    DevBuf lane_pool;                          // fat hash tables of the lane parser (parse_lane.cuh), never cleared per call
+    uint32_t lane_epoch = 0;                   // epoch of the pool's most recent launch (0 = pool all-empty)
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -107,6 +112,57 @@ snappy_b200_status default_ctx(snappy_b200_ctx** out) {
     return SNAPPY_B200_OK;
 }
 
+// ---- exact parse: which kernel --------------------------------------------------------------------
+// mode 0 (SNAPPY_B200_EXACT) picks by shape: the lane parser (one thread per fragment, all fragments in
+// flight, parse_lane.cuh) when the call has enough fragments to hide DRAM latency behind their number,
+// the pipelined parser (one CTA per fragment, parse_pipe.cuh) otherwise.  Modes 5 / 6 force one or the
+// other (tests, A/B runs); both produce the reference's bytes.
+constexpr int kModeLane = 5, kModePipe = 6;
+constexpr size_t kLanePoolMaxBytes = 20ull << 30;
+inline uint32_t lane_min_frags() {
+    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 3072u; }();
+    return v;
+}
+inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
+    if (mode == kModeLane) return true;
+    return mode == SNAPPY_B200_EXACT && job_len == sb::kBlock && n_jobs >= lane_min_frags() &&
+           sb::lane_pool_bytes(n_jobs, job_len) <= kLanePoolMaxBytes;
+}
+inline int kernel_mode(int mode) { return mode == kModePipe ? (int)SNAPPY_B200_EXACT : mode; }
+
+// Reserve the pool for `n_jobs` tables and open a new epoch (stream-ordered on c->stream).
+snappy_b200_status lane_begin(snappy_b200_ctx* c, uint64_t n_jobs, uint32_t job_len, uint32_t* epoch) {
+    const size_t need = sb::lane_pool_bytes(n_jobs, job_len);
+    const bool fresh = need > c->lane_pool.cap;
+    CU(c->lane_pool.reserve(need));
+    if (fresh || c->lane_epoch >= 65535u) {                  // new memory, or the 16-bit epoch would repeat
+        CU(cudaMemsetAsync(c->lane_pool.p, 0, c->lane_pool.cap, c->stream));
+        c->lane_epoch = 0;
+    }
+    *epoch = ++c->lane_epoch;
+    return SNAPPY_B200_OK;
+}
+
+// Parse + sizes of all jobs of `p` on c->stream, in waves if the pool cap is smaller than the batch.
+snappy_b200_status lane_parse_all(snappy_b200_ctx* c, const sb::JobParams& p) {
+    const size_t per_job = sb::lane_pool_bytes(1, p.job_len);
+    uint64_t per_wave = kLanePoolMaxBytes / per_job;
+    if (per_wave > p.n_jobs) per_wave = p.n_jobs;
+    for (uint64_t j0 = 0; j0 < p.n_jobs; j0 += per_wave) {
+        sb::JobParams q = p;
+        q.in += j0 * p.in_stride;
+        q.n_total -= j0 * p.in_stride;
+        q.seqs += j0 * sb::seq_stride(p.job_len);
+        q.nseq += j0;
+        q.sizes += j0;
+        q.n_jobs = (uint32_t)(p.n_jobs - j0 < per_wave ? p.n_jobs - j0 : per_wave);
+        uint32_t epoch = 0;
+        if (lane_begin(c, q.n_jobs, p.job_len, &epoch) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+        CU(sb::launch_parse_lane(q, c->lane_pool.p, epoch, c->stream, &c->launches));
+    }
+    return SNAPPY_B200_OK;
+}
+
 // Stream / fragment-range compression with input and output on the device.
 snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst,
                                 size_t dst_cap, unsigned long long* d_out_n, int mode,
@@ -114,7 +170,8 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     const bool with_header = framing == 1, framed = framing == 2;
     if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
     if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */ &&
-        mode != 3 /* exact, single-warp window parser */ && mode != 4 /* exact, pipelined, input in smem */)
+        mode != 3 /* exact, single-warp window parser */ && mode != 4 /* exact, pipelined, input in smem */ &&
+        mode != kModeLane && mode != kModePipe)
         return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
     if (dst_cap < (framed ? snappy_b200_frame_max_length(n) : snappy_b200_max_compressed_length(n)))
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max length of the output");
@@ -142,11 +199,13 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.out = (uint8_t*)d_dst + (framed ? 8 : 0);
     p.out_stride = 0;
     p.offsets = (const unsigned long long*)c->offsets.p;
+    const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
     CU(cudaEventRecord(c->evp0, c->stream));
-    CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
+    else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    CU(sb::launch_size(p, c->stream, &c->launches));
+    if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));   // the lane parser adds up sizes as it goes
     if (framed) {
         CU(sb::launch_frame_bump((uint32_t*)c->sizes.p, n_frag, c->stream, &c->launches));
         CU(sb::launch_crc32c_chunks((const uint8_t*)d_src, nullptr, nullptr, sb::kBlock, n, sb::kBlock, n_frag,
@@ -164,13 +223,19 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     return SNAPPY_B200_OK;
 }
 
-constexpr size_t kMaxChunks = 1024;
 constexpr size_t kPipeMinBytes = 24u << 20;     // below this one H2D + one D2H is as good as it gets
 
 // Chunk size of the host pipeline: whole fragments; large inputs use 64 MiB (1024 fragments, a
 // little more than one resident wave of the pipelined parser), smaller ones an eighth.
-size_t pipe_chunk_bytes(size_t n, bool fast) {
+size_t pipe_chunk_bytes(size_t n, bool fast, bool lane) {
     static const size_t env = [] { const char* e = getenv("SNAPPY_B200_CHUNK_MIB"); return e ? (size_t)atol(e) << 20 : (size_t)0; }();
+    if (lane && !env) {
+        // a lane-parser launch takes the same time whatever its size (every fragment is its own chain),
+        // so chunks only set how early the first one starts: 32 MiB = 0.6 ms of PCIe each, one stream each
+        size_t c = 32u << 20;
+        while ((n + c - 1) / c > kMaxChunks) c *= 2;
+        return c;
+    }
     // measured on 1 GiB text (8 parse streams): exact 16 MiB 36.0 ms, 32 MiB 36.4, 8 MiB 44; fast 32 MiB 21.2 ms, 16 MiB 22.6
     size_t c = env ? env : (n >= (256u << 20) ? (fast ? (32u << 20) : (16u << 20)) : n / 8);
     c = (c + sb::kBlock - 1) / sb::kBlock * sb::kBlock;
@@ -211,9 +276,10 @@ snappy_b200_status ensure_pipe(snappy_b200_ctx* c, size_t n_chunks) {
 snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* src, size_t n,
                                            uint8_t* dst, size_t dst_cap, size_t* out_n, int mode) {
     const size_t cap = snappy_b200_max_compressed_length(n);
-    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST);
-    const size_t n_chunks = (n + chunk - 1) / chunk;
     const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
+    const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
+    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane);
+    const size_t n_chunks = (n + chunk - 1) / chunk;
     const uint32_t hdr = sb::varint32_len((uint32_t)n);
     if (ensure_pipe(c, n_chunks) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(c->d_in.reserve(n + 64));
@@ -224,6 +290,9 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     CU(c->offsets.reserve((size_t)(n_frag + 1) * sizeof(unsigned long long)));
     uint8_t* d_in = (uint8_t*)c->d_in.p;
     uint8_t* d_out = (uint8_t*)c->d_out.p;
+    uint32_t lane_epoch = 0;
+    if (lane && lane_begin(c, n_frag, sb::kBlock, &lane_epoch) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    const int n_ps = lane ? kParseStreams : pipe_streams();
     // nothing of this call may overtake earlier work on the context's stream (shared scratch)
     CU(cudaEventRecord(c->ev_start, c->stream));
     CU(cudaStreamWaitEvent(c->s_h2d, c->ev_start, 0));
@@ -254,12 +323,15 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         p.out = d_out;
         p.out_stride = 0;
         p.offsets = (const unsigned long long*)c->offsets.p + f0;
-        cudaStream_t ps = c->s_parse[k % pipe_streams()];
+        cudaStream_t ps = c->s_parse[k % n_ps];
         CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
-        CU(sb::launch_parse(p, mode, ps, &c->launches));
+        if (lane)
+            CU(sb::launch_parse_lane(p, (uint8_t*)c->lane_pool.p + sb::lane_pool_bytes(f0, sb::kBlock), lane_epoch, ps,
+                                     &c->launches));
+        else CU(sb::launch_parse(p, kernel_mode(mode), ps, &c->launches));
         CU(cudaEventRecord(c->ev_p[k], ps));
         CU(cudaStreamWaitEvent(es, c->ev_p[k], 0));
-        CU(sb::launch_size(p, es, &c->launches));
+        if (!lane) CU(sb::launch_size(p, es, &c->launches));
         CU(sb::launch_scan(p.sizes, p.n_jobs, (unsigned long long*)c->offsets.p + f0, k == 0 ? hdr : 0,
                            (uint32_t)n, d_out, c->d_total, es, &c->launches,
                            k == 0 ? nullptr : c->d_total, c->h_run_dev + k));
@@ -351,7 +423,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->seqs.release(); c->nseq.release(); c->sizes.release(); c->offsets.release();
-    c->d_in.release(); c->d_out.release();
+    c->d_in.release(); c->d_out.release(); c->lane_pool.release();
     c->crcs.release(); c->frame_ix.release(); c->frame_res.release(); c->raw_ix.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
@@ -451,11 +523,13 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.out = (uint8_t*)d_dst;
     p.out_stride = out_stride;
     p.offsets = nullptr;
+    const bool lane = lane_chosen(mode, count, (uint32_t)len);
     CU(cudaEventRecord(c->evp0, c->stream));
-    CU(sb::launch_parse(p, mode, c->stream, &c->launches));
+    if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
+    else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    CU(sb::launch_size(p, c->stream, &c->launches));
+    if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));
     CU(sb::launch_emit(p, c->stream, &c->launches));
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;

@@ -15,6 +15,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "parse_window.cuh"
 #include "parse_pipe.cuh"
 #include "parse_fast.cuh"
+#include "parse_lane.cuh"
 #include "emit.cuh"
 #include "decode.cuh"
 #include "decode_par.cuh"
@@ -404,6 +405,39 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
     else if (mode == 4)
         parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);
     else parse_kernel<true><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- lane parser -----------------------------------------------------------------------------------
+size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
+    return (size_t)n_jobs * table_entries(job_len) * kLaneEntryBytes;
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
+                              unsigned long long* launches) {
+    if (p.n_jobs == 0) return cudaSuccess;
+    static_assert(sizeof(lane::Entry) == kLaneEntryBytes, "entry size");
+    // tuning knobs (measured defaults): fragments per warp and table prefetch variant
+    static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0), pf = env_int("SNAPPY_B200_LANE_PF", 1);
+    LaneTable t;
+    t.base = reinterpret_cast<lane::Entry*>(pool);
+    t.stride = table_entries(p.job_len);
+    t.epoch = epoch;
+    t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 8u;
+    const uint32_t grid = (p.n_jobs + t.fpw - 1) / t.fpw;
+    switch (pf) {
+        case 0: parse_lane_kernel<0><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+        case 3: parse_lane_kernel<3><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+        case 5: parse_lane_kernel<5><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+        case 11: parse_lane_kernel<11><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+        default: parse_lane_kernel<1><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+    }
     if (launches) ++*launches;
     return cudaGetLastError();
 }

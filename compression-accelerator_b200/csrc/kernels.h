@@ -46,6 +46,14 @@ struct JobParams {
 };
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned long long* launches);
+
+// Lane parser (parse_lane.cuh): one thread per job, all jobs in flight, "fat" hash-table entries in a
+// pool in global memory that is never cleared between launches (entries carry the launch's epoch).
+// Writes seqs, nseq AND sizes (no size pass).  pool must hold lane_pool_bytes(n_jobs, job_len) bytes.
+constexpr uint32_t kLaneEntryBytes = 16;
+size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len);
+cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
+                              unsigned long long* launches);
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 

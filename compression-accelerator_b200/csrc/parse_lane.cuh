@@ -1,0 +1,268 @@
+// parse_lane.cuh -- exact greedy parse, ONE THREAD per fragment, every fragment of the call in
+// flight at once ("lane parser").
+//
+// Why: Snappy's parse (tests/snappy/snappy.cc:539-671) is one loop-carried step per ~4.6 input
+// bytes on text, and each step is a chain of dependent memory round trips (own bytes -> hash ->
+// table -> candidate bytes -> compare).  A warp or a CTA per fragment does not shorten that chain,
+// it only spends 32..160 threads' issue slots on it, and the 32 KB shared-memory table caps an SM at
+// six fragments (888 per GPU).  Here the chain is cut to ONE round trip per step and the number of
+// chains in flight is the number of fragments of the call (16,384 per GiB):
+//
+//   * the hash table lives in global memory and every entry is "fat": 16 bytes = position, epoch and
+//     the 12 input bytes at that position.  The 4-byte hit test (snappy.cc:607-608, :656) and the
+//     first 8 bytes of FindMatchLength (snappy-internal.h:95-143) are answered by the entry itself,
+//     so no second, dependent load of the candidate's bytes is needed unless a match is longer than
+//     12 bytes.  A 16-byte entry costs the same 32-byte DRAM sector as a 2-byte one.
+//   * the table is never cleared: an entry is valid only if its epoch equals the call's epoch
+//     (snappy.cc:478 zeroes the table per fragment; an invalid entry reads as "position 0", which
+//     is what a zero entry means to the reference, SURVEY.md 8a item 1, with the fragment's first 12
+//     bytes as its data).
+//   * the thread keeps ip / skip / next_emit in registers and pushes one sequence record per copy;
+//     it also adds up the encoded size of its fragment, so no size pass re-reads the records.
+//
+// Throughput is (fragments in flight) x (bytes per step) / (DRAM latency), bounded by the random
+// 32-byte sector traffic of the tables (one read + one write-back per probe).  Streams with few
+// fragments keep the pipelined parser (parse_pipe.cuh), whose per-fragment latency is lower.
+//
+// The per-fragment routine below is plain C++ over a memory policy, so that the same source is
+// compiled for the host by tests/host_lane (g++) and checked against the reference Snappy byte for
+// byte without a GPU; the product only ever runs the device instantiation.
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __CUDACC__
+#define SB_HD __host__ __device__ __forceinline__
+#else
+#define SB_HD inline
+#endif
+
+namespace sb {
+namespace lane {
+
+typedef unsigned long long seq64;
+
+constexpr uint32_t kLaneMul = 0x1e35a7bdu;     // tests/snappy/snappy.cc:92
+constexpr uint32_t kLaneMargin = 15;           // snappy.cc:556 kInputMarginBytes
+constexpr uint32_t kLaneMaxTable = 16384;      // snappy.h:199-200
+
+struct W3 { uint32_t x, y, z; };               // 12 consecutive input bytes, little endian
+struct Entry { uint32_t tag, g0, g1, g2; };    // tag = position | epoch << 16; g* = bytes at position
+
+SB_HD uint32_t fsr(uint32_t lo, uint32_t hi, uint32_t sh) {   // (hi:lo) >> sh, sh in {0,8,16,24}
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
+#endif
+}
+SB_HD uint32_t ctz64(unsigned long long x) {
+#ifdef __CUDA_ARCH__
+    return (uint32_t)(__ffsll((long long)x) - 1);
+#else
+    return (uint32_t)__builtin_ctzll(x);
+#endif
+}
+
+// sizes of the elements EmitLiteral / EmitCopy produce (snappy.cc:337-431), for the running total
+SB_HD uint32_t enc_literal(uint32_t len) {                    // len >= 1, <= 65536
+    const uint32_t n = len - 1;
+    return len + (n < 60 ? 1u : n < 256 ? 2u : 3u);
+}
+SB_HD uint32_t enc_copy(uint32_t offset, uint32_t len) {
+    if (len < 12) return offset < 2048 ? 2u : 3u;
+    const uint32_t k = (len >= 68) ? ((len - 4) >> 6) : 0u;   // 64-byte copies
+    uint32_t rest = len - (k << 6), n = 3 * k;
+    if (rest > 64) { n += 3; rest -= 60; }
+    return n + ((rest < 12 && offset < 2048) ? 2u : 3u);
+}
+SB_HD seq64 pack_seq(uint32_t lit, uint32_t len, uint32_t off) {   // kernels.h seq_t layout
+    return (seq64)lit | ((seq64)len << 17) | ((seq64)off << 33);
+}
+
+struct Out {
+    seq64* seqs;
+    uint32_t n, bytes;
+};
+
+// 12 bytes at src[p..p+12) from four aligned words (the address may have any alignment).  Touches
+// only words that hold at least one byte of [p, p+13).
+template <class M>
+SB_HD W3 load12(const uint8_t* src, uint32_t p) {
+    const uintptr_t a = (uintptr_t)(src + p);
+    const uint32_t* w = (const uint32_t*)(a & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(a & 3u) << 3;
+    const uint32_t w0 = M::ld_in(w), w1 = M::ld_in(w + 1), w2 = M::ld_in(w + 2), w3 = M::ld_in(w + 3);
+    W3 r;
+    r.x = fsr(w0, w1, sh); r.y = fsr(w1, w2, sh); r.z = fsr(w2, w3, sh);
+    return r;
+}
+template <class M>
+SB_HD uint32_t load4(const uint8_t* src, uint32_t p) {
+    const uintptr_t a = (uintptr_t)(src + p);
+    const uint32_t* w = (const uint32_t*)(a & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(a & 3u) << 3;
+    const uint32_t w0 = M::ld_in(w);
+    return sh ? fsr(w0, M::ld_in(w + 1), sh) : w0;
+}
+
+// Common prefix of src[a..] and src[b..] (a < b), b bounded by len: the part of FindMatchLength
+// (snappy-internal.h:95-143) the fat entry could not answer.  Rare on text (matches > 12 bytes).
+template <class M>
+SB_HD uint32_t extend_slow(const uint8_t* src, uint32_t a, uint32_t b, uint32_t len) {
+    uint32_t n = 0;
+    while (b + n + 4 <= len) {
+        const uint32_t x = load4<M>(src, a + n) ^ load4<M>(src, b + n);
+        if (x) return n + (ctz64((unsigned long long)x) >> 3);
+        n += 4;
+    }
+    while (b + n < len && M::ld_byte(src + a + n) == M::ld_byte(src + b + n)) ++n;
+    return n;
+}
+
+template <class M>
+SB_HD void push(Out& o, uint32_t lit, uint32_t len, uint32_t off) {
+    M::st_seq(o.seqs + o.n, pack_seq(lit, len, off));
+    ++o.n;
+    o.bytes += (lit ? enc_literal(lit) : 0u) + (len ? enc_copy(off, len) : 0u);
+}
+
+// kPf: bit 0 = prefetch the table sector of the next scan position (the miss path),
+//      bits 1.. = number of hit-path positions (p+4 ...) whose table sector is prefetched.
+template <class M, int kPf>
+SB_HD void parse_fragment(const uint8_t* src, uint32_t len, Entry* table, uint32_t shift, uint32_t epoch,
+                          Out& out) {
+    uint32_t next_emit = 0;
+    if (len >= kLaneMargin) {                                   // snappy.cc:557
+        const uint32_t ip_limit = len - kLaneMargin;            // snappy.cc:558
+        const uint32_t etag = epoch << 16;
+        const W3 f0 = load12<M>(src, 0);                         // what an empty entry stands for
+        uint32_t p = 1, skip = 32;                               // snappy.cc:560, :587
+        bool chain = false;                                      // probe right after a copy (snappy.cc:649-656)
+        for (;;) {
+            uint32_t next;
+            if (!chain) {                                        // scan probe (snappy.cc:589-606)
+                const uint32_t step = skip >> 5;
+                skip += step;
+                next = p + step;
+                if (next > ip_limit) break;
+            } else {                                             // a failed chain probe restarts the scan at ip+1
+                next = p + 1;
+                skip = 32;
+            }
+            const W3 own = load12<M>(src, p);
+            const uint32_t h = (own.x * kLaneMul) >> shift;
+            Entry* slot = table + h;
+            Entry e = M::ld_tab(slot);
+            M::prefetch_in(src, p + 192u, len);
+            if (kPf & 1) {                                       // the next probe if this one misses
+                const uint32_t g1 = (next == p + 1) ? fsr(own.x, own.y, 8) : load4<M>(src, next);
+                M::prefetch_tab(table + ((g1 * kLaneMul) >> shift));
+            }
+            constexpr int kHit = kPf >> 1;                       // the probe after a short copy: ip = p+4 .. p+8
+            if (kHit > 0) M::prefetch_tab(table + ((own.y * kLaneMul) >> shift));
+            if (kHit > 1) M::prefetch_tab(table + ((fsr(own.y, own.z, 8) * kLaneMul) >> shift));
+            if (kHit > 2) M::prefetch_tab(table + ((fsr(own.y, own.z, 16) * kLaneMul) >> shift));
+            if (kHit > 3) M::prefetch_tab(table + ((fsr(own.y, own.z, 24) * kLaneMul) >> shift));
+            if (kHit > 4) M::prefetch_tab(table + ((own.z * kLaneMul) >> shift));
+            uint32_t cand = e.tag & 0xffffu;
+            if ((e.tag >> 16) != epoch) { cand = 0; e.g0 = f0.x; e.g1 = f0.y; e.g2 = f0.z; }
+            Entry mine;
+            mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
+            M::st_tab(slot, mine);                               // snappy.cc:606 / :655
+            if (own.x != e.g0) {                                 // snappy.cc:607-608 / :656
+                p = next;
+                chain = false;
+                continue;
+            }
+            // a copy (snappy.cc:627-641)
+            const unsigned long long x = ((unsigned long long)(own.z ^ e.g2) << 32) | (own.y ^ e.g1);
+            uint32_t matched;
+            if (x) matched = 4 + (ctz64(x) >> 3);
+            else matched = 12 + extend_slow<M>(src, cand + 12, p + 12, len);
+            push<M>(out, p - next_emit, matched, p - cand);
+            p += matched;
+            next_emit = p;
+            if (p >= ip_limit) break;                            // snappy.cc:643-645
+            const W3 prev = load12<M>(src, p - 1);               // snappy.cc:649-651: insert ip-1
+            Entry ins;
+            ins.tag = (p - 1) | etag; ins.g0 = prev.x; ins.g1 = prev.y; ins.g2 = prev.z;
+            M::st_tab(table + ((prev.x * kLaneMul) >> shift), ins);
+            chain = true;
+        }
+    }
+    if (next_emit < len) push<M>(out, len - next_emit, 0, 0);    // snappy.cc:665-668
+}
+
+// table entries of a fragment of `len` bytes (snappy.cc:445-456) and the matching hash shift
+SB_HD uint32_t entries_for(uint32_t len) {
+    if (len > kLaneMaxTable) return kLaneMaxTable;
+    uint32_t e = 256;
+    while (e < len) e <<= 1;
+    return e;
+}
+SB_HD uint32_t shift_for(uint32_t entries) {
+    uint32_t lg = 0;
+    while ((1u << lg) < entries) ++lg;
+    return 32u - lg;
+}
+
+}  // namespace lane
+}  // namespace sb
+
+#ifdef __CUDACC__
+#include "kernels.h"
+#include "emit.cuh"
+
+namespace sb {
+
+struct LaneDev {                                                  // device memory policy
+    static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return __ldg(p); }
+    static __device__ __forceinline__ uint32_t ld_byte(const uint8_t* p) { return __ldg(p); }
+    static __device__ __forceinline__ lane::Entry ld_tab(const lane::Entry* p) {
+        const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));      // L2 only: a random sector, no reuse in L1
+        lane::Entry e; e.tag = v.x; e.g0 = v.y; e.g1 = v.z; e.g2 = v.w;
+        return e;
+    }
+    static __device__ __forceinline__ void st_tab(lane::Entry* p, const lane::Entry& e) {
+        __stcg(reinterpret_cast<uint4*>(p), make_uint4(e.tag, e.g0, e.g1, e.g2));
+    }
+    static __device__ __forceinline__ void st_seq(lane::seq64* p, lane::seq64 v) { __stcg(p, v); }
+    static __device__ __forceinline__ void prefetch_tab(const lane::Entry* p) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    }
+    static __device__ __forceinline__ void prefetch_in(const uint8_t* src, uint32_t pos, uint32_t len) {
+        if (pos < len) asm volatile("prefetch.global.L1 [%0];" ::"l"(src + pos));
+    }
+};
+
+struct LaneTable {
+    lane::Entry* base;         // job j uses base + j * stride entries
+    uint32_t stride;           // entries per job = table_entries(job_len)
+    uint32_t epoch;            // 1..65535, never repeated between two clears of the pool
+    uint32_t fpw;              // fragments (active lanes) per warp
+};
+
+constexpr int kLaneThreads = 32;
+
+template <int kPf>
+__global__ void __launch_bounds__(kLaneThreads) parse_lane_kernel(JobParams p, LaneTable t) {
+    const uint32_t lane_id = threadIdx.x & 31u;
+    if (lane_id >= t.fpw) return;
+    const uint32_t warp = blockIdx.x * (kLaneThreads / 32) + (threadIdx.x >> 5);
+    const uint32_t job = warp * t.fpw + lane_id;
+    if (job >= p.n_jobs) return;
+    const uint32_t len = job_len_of(p, job);
+    const uint32_t entries = lane::entries_for(len);             // from THIS fragment's length
+    lane::Out out;
+    out.seqs = p.seqs + (uint64_t)job * seq_stride(p.job_len);
+    out.n = 0;
+    out.bytes = p.with_header ? varint32_len(len) : 0u;
+    lane::parse_fragment<LaneDev, kPf>(p.in + (uint64_t)job * p.in_stride, len,
+                                       t.base + (uint64_t)job * t.stride, 32u - (31u - __clz(entries)), t.epoch, out);
+    p.nseq[job] = out.n;
+    p.sizes[job] = out.bytes;
+}
+
+}  // namespace sb
+#endif  // __CUDACC__
