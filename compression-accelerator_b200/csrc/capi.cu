@@ -401,6 +401,10 @@ snappy_b200_status snappy_b200_create(snappy_b200_ctx** out, int device) {
         return fail(SNAPPY_B200_NO_DEVICE, "no CUDA device (libsnappy_b200 has no CPU path)", e);
     if (device < 0 || device >= count) return fail(SNAPPY_B200_INVALID_INPUT, "bad device ordinal");
     CU(cudaSetDevice(device));
+    {   // experiment knob: L2 <- DRAM fetch granularity (32 / 64 / 128 bytes); unset = driver default
+        const char* e = getenv("SNAPPY_B200_L2_FETCH");
+        if (e && atoi(e) > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
+    }
     std::call_once(g_init_once, [] { g_init_err = sb::kernels_init(); });
     if (g_init_err != cudaSuccess) return fail(SNAPPY_B200_CUDA_ERROR, "kernels_init", g_init_err);
     snappy_b200_ctx* c = new (std::nothrow) snappy_b200_ctx;

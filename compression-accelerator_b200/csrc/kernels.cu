@@ -410,34 +410,35 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
 }
 
 // ---- lane parser -----------------------------------------------------------------------------------
-size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
-    return (size_t)n_jobs * table_entries(job_len) * kLaneEntryBytes;
-}
-
 static int env_int(const char* name, int dflt) {
     const char* e = getenv(name);
     return e ? atoi(e) : dflt;
+}
+// tuning knobs: SNAPPY_B200_LANE_VAR = kVar bits of parse_lane.cuh, SNAPPY_B200_LANE_FPW = fragments per warp
+static int lane_var() { static const int v = env_int("SNAPPY_B200_LANE_VAR", 2); return v; }
+
+size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
+    return (size_t)n_jobs * table_entries(job_len) * ((lane_var() & 8) ? 32u : 16u);
 }
 
 cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
                               unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
     static_assert(sizeof(lane::Entry) == kLaneEntryBytes, "entry size");
-    // tuning knobs (measured defaults): fragments per warp and table prefetch variant
-    static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0), pf = env_int("SNAPPY_B200_LANE_PF", 1);
+    static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0);
     LaneTable t;
-    t.base = reinterpret_cast<lane::Entry*>(pool);
+    t.base = reinterpret_cast<uint8_t*>(pool);
     t.stride = table_entries(p.job_len);
     t.epoch = epoch;
     t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 8u;
     const uint32_t grid = (p.n_jobs + t.fpw - 1) / t.fpw;
-    switch (pf) {
-        case 0: parse_lane_kernel<0><<<grid, kLaneThreads, 0, st>>>(p, t); break;
-        case 3: parse_lane_kernel<3><<<grid, kLaneThreads, 0, st>>>(p, t); break;
-        case 5: parse_lane_kernel<5><<<grid, kLaneThreads, 0, st>>>(p, t); break;
-        case 11: parse_lane_kernel<11><<<grid, kLaneThreads, 0, st>>>(p, t); break;
-        default: parse_lane_kernel<1><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+#define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+    switch (lane_var()) {
+        SB_LANE_CASE(0) SB_LANE_CASE(1) SB_LANE_CASE(2) SB_LANE_CASE(4) SB_LANE_CASE(6) SB_LANE_CASE(8)
+        SB_LANE_CASE(10) SB_LANE_CASE(12) SB_LANE_CASE(14) SB_LANE_CASE(16) SB_LANE_CASE(18) SB_LANE_CASE(9)
+        default: return cudaErrorInvalidValue;
     }
+#undef SB_LANE_CASE
     if (launches) ++*launches;
     return cudaGetLastError();
 }

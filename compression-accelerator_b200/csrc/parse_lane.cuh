@@ -127,11 +127,16 @@ SB_HD void push(Out& o, uint32_t lit, uint32_t len, uint32_t off) {
     o.bytes += (lit ? enc_literal(lit) : 0u) + (len ? enc_copy(off, len) : 0u);
 }
 
-// kPf: bit 0 = prefetch the table sector of the next scan position (the miss path),
-//      bits 1.. = number of hit-path positions (p+4 ...) whose table sector is prefetched.
-template <class M, int kPf>
-SB_HD void parse_fragment(const uint8_t* src, uint32_t len, Entry* table, uint32_t shift, uint32_t epoch,
+// kVar selects how the table is reached (all variants produce the same records):
+//   bit 0  prefetch.global.L2 of the next scan position's entry (fetches a 128-byte line)
+//   bit 1  speculative LOAD of the next scan position's entry into registers (one 32-byte sector); a
+//          missed probe then continues with no memory round trip at all.  The load is issued before
+//          this probe's own store, so if both hash to the same slot the entry just stored is used.
+//   bits 2.. belong to the memory policy (store ordering, entry stride, cache path).
+template <class M, int kVar>
+SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_t shift, uint32_t epoch,
                           Out& out) {
+    constexpr bool kPfL2 = (kVar & 1) != 0, kSpec = (kVar & 2) != 0;
     uint32_t next_emit = 0;
     if (len >= kLaneMargin) {                                   // snappy.cc:557
         const uint32_t ip_limit = len - kLaneMargin;            // snappy.cc:558
@@ -139,6 +144,9 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, Entry* table, uint32
         const W3 f0 = load12<M>(src, 0);                         // what an empty entry stands for
         uint32_t p = 1, skip = 32;                               // snappy.cc:560, :587
         bool chain = false;                                      // probe right after a copy (snappy.cc:649-656)
+        bool have_spec = false;
+        uint32_t h_prev = 0;
+        Entry spec = {0, 0, 0, 0}, mine_prev = {0, 0, 0, 0};
         for (;;) {
             uint32_t next;
             if (!chain) {                                        // scan probe (snappy.cc:589-606)
@@ -152,27 +160,26 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, Entry* table, uint32
             }
             const W3 own = load12<M>(src, p);
             const uint32_t h = (own.x * kLaneMul) >> shift;
-            Entry* slot = table + h;
-            Entry e = M::ld_tab(slot);
+            void* slot = M::slot(table, h);
+            Entry e;
+            if (kSpec && have_spec) e = (h == h_prev) ? mine_prev : spec;
+            else e = M::ld_tab(slot);
             M::prefetch_in(src, p + 192u, len);
-            if (kPf & 1) {                                       // the next probe if this one misses
+            if (kPfL2 || kSpec) {                                // the next probe if this one misses
                 const uint32_t g1 = (next == p + 1) ? fsr(own.x, own.y, 8) : load4<M>(src, next);
-                M::prefetch_tab(table + ((g1 * kLaneMul) >> shift));
+                void* slot1 = M::slot(table, (g1 * kLaneMul) >> shift);
+                if (kSpec) spec = M::ld_tab(slot1);
+                else M::prefetch_tab(slot1);
             }
-            constexpr int kHit = kPf >> 1;                       // the probe after a short copy: ip = p+4 .. p+8
-            if (kHit > 0) M::prefetch_tab(table + ((own.y * kLaneMul) >> shift));
-            if (kHit > 1) M::prefetch_tab(table + ((fsr(own.y, own.z, 8) * kLaneMul) >> shift));
-            if (kHit > 2) M::prefetch_tab(table + ((fsr(own.y, own.z, 16) * kLaneMul) >> shift));
-            if (kHit > 3) M::prefetch_tab(table + ((fsr(own.y, own.z, 24) * kLaneMul) >> shift));
-            if (kHit > 4) M::prefetch_tab(table + ((own.z * kLaneMul) >> shift));
             uint32_t cand = e.tag & 0xffffu;
             if ((e.tag >> 16) != epoch) { cand = 0; e.g0 = f0.x; e.g1 = f0.y; e.g2 = f0.z; }
             Entry mine;
             mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
-            M::st_tab(slot, mine);                               // snappy.cc:606 / :655
+            M::st_tab(slot, mine, e.tag);                        // snappy.cc:606 / :655
             if (own.x != e.g0) {                                 // snappy.cc:607-608 / :656
                 p = next;
                 chain = false;
+                if (kSpec) { have_spec = true; h_prev = h; mine_prev = mine; }
                 continue;
             }
             // a copy (snappy.cc:627-641)
@@ -187,8 +194,9 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, Entry* table, uint32
             const W3 prev = load12<M>(src, p - 1);               // snappy.cc:649-651: insert ip-1
             Entry ins;
             ins.tag = (p - 1) | etag; ins.g0 = prev.x; ins.g1 = prev.y; ins.g2 = prev.z;
-            M::st_tab(table + ((prev.x * kLaneMul) >> shift), ins);
+            M::st_tab(M::slot(table, (prev.x * kLaneMul) >> shift), ins, 0u);
             chain = true;
+            have_spec = false;
         }
     }
     if (next_emit < len) push<M>(out, len - next_emit, 0, 0);    // snappy.cc:665-668
@@ -216,19 +224,39 @@ SB_HD uint32_t shift_for(uint32_t entries) {
 
 namespace sb {
 
-struct LaneDev {                                                  // device memory policy
+// Device memory policy.  kVar bits (continued from parse_fragment):
+//   bit 2  the store waits for the load of the same slot (register dependency) instead of chasing it
+//   bit 3  entries padded to 32 bytes and written with ONE 256-bit store (a full DRAM sector, so the
+//          L2 never has to merge a partial write with a fill)
+//   bit 4  table loads through L1 (ld.global.ca) instead of L2-only
+template <int kVar>
+struct LaneDev {
+    static constexpr uint32_t kStride = (kVar & 8) ? 32u : 16u;
     static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return __ldg(p); }
     static __device__ __forceinline__ uint32_t ld_byte(const uint8_t* p) { return __ldg(p); }
-    static __device__ __forceinline__ lane::Entry ld_tab(const lane::Entry* p) {
-        const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));      // L2 only: a random sector, no reuse in L1
+    static __device__ __forceinline__ void* slot(void* table, uint32_t h) {
+        return reinterpret_cast<uint8_t*>(table) + (size_t)h * kStride;
+    }
+    static __device__ __forceinline__ lane::Entry ld_tab(const void* p) {
+        uint4 v;
+        if (kVar & 16) asm volatile("ld.global.ca.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        else v = __ldcg(reinterpret_cast<const uint4*>(p));     // L2 only: a random sector, no reuse in L1
         lane::Entry e; e.tag = v.x; e.g0 = v.y; e.g1 = v.z; e.g2 = v.w;
         return e;
     }
-    static __device__ __forceinline__ void st_tab(lane::Entry* p, const lane::Entry& e) {
-        __stcg(reinterpret_cast<uint4*>(p), make_uint4(e.tag, e.g0, e.g1, e.g2));
+    static __device__ __forceinline__ void st_tab(void* p, const lane::Entry& e, uint32_t dep) {
+        uint32_t tag = e.tag;
+        if (kVar & 4) asm volatile("" : "+r"(tag) : "r"(dep));
+        if (kVar & 8) {
+            asm volatile("st.global.cg.v8.b32 [%0], {%1,%2,%3,%4,%5,%5,%5,%5};" ::"l"(p), "r"(tag), "r"(e.g0),
+                         "r"(e.g1), "r"(e.g2), "r"(0u)
+                         : "memory");
+        } else {
+            __stcg(reinterpret_cast<uint4*>(p), make_uint4(tag, e.g0, e.g1, e.g2));
+        }
     }
     static __device__ __forceinline__ void st_seq(lane::seq64* p, lane::seq64 v) { __stcg(p, v); }
-    static __device__ __forceinline__ void prefetch_tab(const lane::Entry* p) {
+    static __device__ __forceinline__ void prefetch_tab(const void* p) {
         asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     }
     static __device__ __forceinline__ void prefetch_in(const uint8_t* src, uint32_t pos, uint32_t len) {
@@ -237,7 +265,7 @@ struct LaneDev {                                                  // device memo
 };
 
 struct LaneTable {
-    lane::Entry* base;         // job j uses base + j * stride entries
+    uint8_t* base;             // job j uses base + j * stride * (bytes per entry)
     uint32_t stride;           // entries per job = table_entries(job_len)
     uint32_t epoch;            // 1..65535, never repeated between two clears of the pool
     uint32_t fpw;              // fragments (active lanes) per warp
@@ -245,7 +273,7 @@ struct LaneTable {
 
 constexpr int kLaneThreads = 32;
 
-template <int kPf>
+template <int kVar>
 __global__ void __launch_bounds__(kLaneThreads) parse_lane_kernel(JobParams p, LaneTable t) {
     const uint32_t lane_id = threadIdx.x & 31u;
     if (lane_id >= t.fpw) return;
@@ -258,8 +286,9 @@ __global__ void __launch_bounds__(kLaneThreads) parse_lane_kernel(JobParams p, L
     out.seqs = p.seqs + (uint64_t)job * seq_stride(p.job_len);
     out.n = 0;
     out.bytes = p.with_header ? varint32_len(len) : 0u;
-    lane::parse_fragment<LaneDev, kPf>(p.in + (uint64_t)job * p.in_stride, len,
-                                       t.base + (uint64_t)job * t.stride, 32u - (31u - __clz(entries)), t.epoch, out);
+    lane::parse_fragment<LaneDev<kVar>, kVar>(p.in + (uint64_t)job * p.in_stride, len,
+                                              t.base + (uint64_t)job * t.stride * LaneDev<kVar>::kStride,
+                                              32u - (31u - __clz(entries)), t.epoch, out);
     p.nseq[job] = out.n;
     p.sizes[job] = out.bytes;
 }

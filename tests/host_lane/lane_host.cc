@@ -18,10 +18,11 @@ namespace {
 struct Host {
     static uint32_t ld_in(const uint32_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
     static uint32_t ld_byte(const uint8_t* p) { return *p; }
-    static sb::lane::Entry ld_tab(const sb::lane::Entry* p) { return *p; }
-    static void st_tab(sb::lane::Entry* p, const sb::lane::Entry& e) { *p = e; }
+    static void* slot(void* table, uint32_t h) { return (sb::lane::Entry*)table + h; }
+    static sb::lane::Entry ld_tab(const void* p) { return *(const sb::lane::Entry*)p; }
+    static void st_tab(void* p, const sb::lane::Entry& e, uint32_t) { *(sb::lane::Entry*)p = e; }
     static void st_seq(sb::lane::seq64* p, sb::lane::seq64 v) { *p = v; }
-    static void prefetch_tab(const sb::lane::Entry* p) { (void)*(volatile const uint32_t*)p; }   // must be a mapped slot
+    static void prefetch_tab(const void* p) { (void)*(volatile const uint32_t*)p; }   // must be a mapped slot
     static void prefetch_in(const uint8_t*, uint32_t, uint32_t) {}
 };
 
@@ -44,7 +45,7 @@ extern "C" {
 
 // Whole stream: varint32(n) + fragments.  One table reused for every fragment with a fresh epoch each
 // time (starting at epoch0), i.e. stale entries of earlier fragments are always present.
-// pf selects the prefetch variant (values the kernel is built with).  Returns the stream length, or 0
+// pf selects the look-ahead variant (kVar bits 0-1 of parse_fragment).  Returns the stream length, or 0
 // if a fragment's running size differs from the encoded size / the records do not cover the fragment.
 size_t lane_host_compress(const uint8_t* in, size_t n, uint8_t* out, int pf, uint32_t epoch0) {
     using namespace sb::lane;
@@ -64,8 +65,7 @@ size_t lane_host_compress(const uint8_t* in, size_t n, uint8_t* out, int pf, uin
         const uint32_t entries = entries_for(len), shift = shift_for(entries);
         if (pf == 0) parse_fragment<Host, 0>(src, len, table.data(), shift, epoch, o);
         else if (pf == 1) parse_fragment<Host, 1>(src, len, table.data(), shift, epoch, o);
-        else if (pf == 5) parse_fragment<Host, 5>(src, len, table.data(), shift, epoch, o);
-        else parse_fragment<Host, 11>(src, len, table.data(), shift, epoch, o);
+        else parse_fragment<Host, 2>(src, len, table.data(), shift, epoch, o);
         epoch = epoch == 65535 ? 1 : epoch + 1;
         if (epoch == epoch0) memset(table.data(), 0, table.size() * sizeof(Entry));
         const size_t op0 = op;

@@ -34,7 +34,7 @@ def lane():
     return compress
 
 
-@pytest.mark.parametrize("pf", [0, 1, 5, 11])
+@pytest.mark.parametrize("pf", [0, 1, 2])
 def test_fixtures(lane, oracle, pf):
     for name in sorted(corpus.manifest()["files"]):
         data = corpus.fixture(name)
@@ -51,14 +51,14 @@ def test_small_lengths_and_kats(lane, oracle):
     for kind in ("random", "real", "repeating"):
         for n in corpus.SWEEP_SIZES:
             data = corpus.benchmark_file(kind, n)
-            assert lane(data, 5) == oracle.compress(data), (kind, n)
+            assert lane(data, 2) == oracle.compress(data), (kind, n)
 
 
 @pytest.mark.parametrize("seed", range(12))
 def test_structured_random(lane, oracle, seed):
     n = [1, 14, 15, 16, 100, 4096, 65535, 65536, 65537, 70000, 200000, 300001][seed]
     data = corpus.structured_random(n, seed)
-    assert lane(data, seed % 2) == oracle.compress(data)
+    assert lane(data, seed % 3) == oracle.compress(data)
 
 
 def test_epoch_wrap_and_stale_entries(lane, oracle):
@@ -66,4 +66,4 @@ def test_epoch_wrap_and_stale_entries(lane, oracle):
     data = corpus.fixture("all-mtg-cards.txt")[:65536 * 6 + 999]
     want = oracle.compress(data)
     for epoch0 in (1, 65533, 65535):
-        assert lane(data, 1, epoch0) == want, epoch0
+        assert lane(data, 2, epoch0) == want, epoch0
