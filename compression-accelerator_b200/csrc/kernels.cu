@@ -415,7 +415,7 @@ static int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 // tuning knobs: SNAPPY_B200_LANE_VAR = kVar bits of parse_lane.cuh, SNAPPY_B200_LANE_FPW = fragments per warp
-static int lane_var() { static const int v = env_int("SNAPPY_B200_LANE_VAR", 2); return v; }
+static int lane_var() { static const int v = env_int("SNAPPY_B200_LANE_VAR", 32); return v; }
 
 size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
     return (size_t)n_jobs * table_entries(job_len) * ((lane_var() & 8) ? 32u : 16u);
@@ -435,7 +435,8 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
 #define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, kLaneThreads, 0, st>>>(p, t); break;
     switch (lane_var()) {
         SB_LANE_CASE(0) SB_LANE_CASE(1) SB_LANE_CASE(2) SB_LANE_CASE(4) SB_LANE_CASE(6) SB_LANE_CASE(8)
-        SB_LANE_CASE(10) SB_LANE_CASE(12) SB_LANE_CASE(14) SB_LANE_CASE(16) SB_LANE_CASE(18) SB_LANE_CASE(9)
+        SB_LANE_CASE(10) SB_LANE_CASE(9) SB_LANE_CASE(32) SB_LANE_CASE(33) SB_LANE_CASE(34) SB_LANE_CASE(40)
+        SB_LANE_CASE(41) SB_LANE_CASE(42)
         default: return cudaErrorInvalidValue;
     }
 #undef SB_LANE_CASE

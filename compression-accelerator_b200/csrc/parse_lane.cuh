@@ -132,11 +132,15 @@ SB_HD void push(Out& o, uint32_t lit, uint32_t len, uint32_t off) {
 //   bit 1  speculative LOAD of the next scan position's entry into registers (one 32-byte sector); a
 //          missed probe then continues with no memory round trip at all.  The load is issued before
 //          this probe's own store, so if both hash to the same slot the entry just stored is used.
-//   bits 2.. belong to the memory policy (store ordering, entry stride, cache path).
+//   bit 5  the probe is ONE 128-bit atomic exchange (old entry out, this position's entry in) instead of a
+//          load followed by a store.  Measured (scripts/probes/randlat2.cu): a store issued right behind
+//          the load of the same slot collapses to 0.8 G probes/s on the whole GPU whatever the
+//          instruction flavour; the exchange sustains 15-19 G/s, a store one iteration late 17 G/s.
+//   bits 2-4 belong to the memory policy (store ordering, entry stride, cache path).
 template <class M, int kVar>
 SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_t shift, uint32_t epoch,
                           Out& out) {
-    constexpr bool kPfL2 = (kVar & 1) != 0, kSpec = (kVar & 2) != 0;
+    constexpr bool kPfL2 = (kVar & 1) != 0, kSpec = (kVar & 2) != 0, kExch = (kVar & 32) != 0;
     uint32_t next_emit = 0;
     if (len >= kLaneMargin) {                                   // snappy.cc:557
         const uint32_t ip_limit = len - kLaneMargin;            // snappy.cc:558
@@ -161,9 +165,18 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
             const W3 own = load12<M>(src, p);
             const uint32_t h = (own.x * kLaneMul) >> shift;
             void* slot = M::slot(table, h);
-            Entry e;
-            if (kSpec && have_spec) e = (h == h_prev) ? mine_prev : spec;
-            else e = M::ld_tab(slot);
+            Entry mine;
+            mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
+            Entry e;                                             // snappy.cc:602-606 / :652-655: look up, then insert
+            if (kSpec && have_spec) {
+                e = (h == h_prev) ? mine_prev : spec;
+                M::st_tab(slot, mine, 0u);
+            } else if (kExch) {
+                e = M::xchg_tab(slot, mine);
+            } else {
+                e = M::ld_tab(slot);
+                M::st_tab(slot, mine, e.tag);
+            }
             M::prefetch_in(src, p + 192u, len);
             if (kPfL2 || kSpec) {                                // the next probe if this one misses
                 const uint32_t g1 = (next == p + 1) ? fsr(own.x, own.y, 8) : load4<M>(src, next);
@@ -173,9 +186,6 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
             }
             uint32_t cand = e.tag & 0xffffu;
             if ((e.tag >> 16) != epoch) { cand = 0; e.g0 = f0.x; e.g1 = f0.y; e.g2 = f0.z; }
-            Entry mine;
-            mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
-            M::st_tab(slot, mine, e.tag);                        // snappy.cc:606 / :655
             if (own.x != e.g0) {                                 // snappy.cc:607-608 / :656
                 p = next;
                 chain = false;
@@ -254,6 +264,15 @@ struct LaneDev {
         } else {
             __stcg(reinterpret_cast<uint4*>(p), make_uint4(tag, e.g0, e.g1, e.g2));
         }
+    }
+    static __device__ __forceinline__ lane::Entry xchg_tab(void* p, const lane::Entry& n) {
+        lane::Entry o;
+        asm volatile("{\n .reg .b128 o, n;\n mov.b128 n, {%4,%5,%6,%7};\n"
+                     " atom.global.relaxed.gpu.exch.b128 o, [%8], n;\n mov.b128 {%0,%1,%2,%3}, o;\n}"
+                     : "=r"(o.tag), "=r"(o.g0), "=r"(o.g1), "=r"(o.g2)
+                     : "r"(n.tag), "r"(n.g0), "r"(n.g1), "r"(n.g2), "l"(p)
+                     : "memory");
+        return o;
     }
     static __device__ __forceinline__ void st_seq(lane::seq64* p, lane::seq64 v) { __stcg(p, v); }
     static __device__ __forceinline__ void prefetch_tab(const void* p) {

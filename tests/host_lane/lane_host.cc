@@ -21,6 +21,9 @@ struct Host {
     static void* slot(void* table, uint32_t h) { return (sb::lane::Entry*)table + h; }
     static sb::lane::Entry ld_tab(const void* p) { return *(const sb::lane::Entry*)p; }
     static void st_tab(void* p, const sb::lane::Entry& e, uint32_t) { *(sb::lane::Entry*)p = e; }
+    static sb::lane::Entry xchg_tab(void* p, const sb::lane::Entry& n) {
+        sb::lane::Entry o = *(sb::lane::Entry*)p; *(sb::lane::Entry*)p = n; return o;
+    }
     static void st_seq(sb::lane::seq64* p, sb::lane::seq64 v) { *p = v; }
     static void prefetch_tab(const void* p) { (void)*(volatile const uint32_t*)p; }   // must be a mapped slot
     static void prefetch_in(const uint8_t*, uint32_t, uint32_t) {}
@@ -65,7 +68,9 @@ size_t lane_host_compress(const uint8_t* in, size_t n, uint8_t* out, int pf, uin
         const uint32_t entries = entries_for(len), shift = shift_for(entries);
         if (pf == 0) parse_fragment<Host, 0>(src, len, table.data(), shift, epoch, o);
         else if (pf == 1) parse_fragment<Host, 1>(src, len, table.data(), shift, epoch, o);
-        else parse_fragment<Host, 2>(src, len, table.data(), shift, epoch, o);
+        else if (pf == 2) parse_fragment<Host, 2>(src, len, table.data(), shift, epoch, o);
+        else if (pf == 32) parse_fragment<Host, 32>(src, len, table.data(), shift, epoch, o);
+        else parse_fragment<Host, 34>(src, len, table.data(), shift, epoch, o);
         epoch = epoch == 65535 ? 1 : epoch + 1;
         if (epoch == epoch0) memset(table.data(), 0, table.size() * sizeof(Entry));
         const size_t op0 = op;
