@@ -129,6 +129,12 @@ inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
            sb::lane_pool_bytes(n_jobs, job_len) <= kLanePoolMaxBytes;
 }
 inline int kernel_mode(int mode) { return mode == kModePipe ? (int)SNAPPY_B200_EXACT : mode; }
+// Fragments of a lane-parsed stream that go to the pipelined parser instead (it runs beside the lane
+// parser; the split makes both finish together: SNAPPY_B200_HYBRID_PIPE_PCT = its share in percent).
+inline uint32_t hybrid_pipe_frags(uint32_t n_frag) {
+    static const int pct = [] { const char* e = getenv("SNAPPY_B200_HYBRID_PIPE_PCT"); return e ? atoi(e) : 45; }();
+    return pct <= 0 ? 0u : (uint32_t)((uint64_t)n_frag * (uint64_t)(pct > 100 ? 100 : pct) / 100u);
+}
 
 // Reserve the pool for `n_jobs` tables and open a new epoch (stream-ordered on c->stream).
 snappy_b200_status lane_begin(snappy_b200_ctx* c, uint64_t n_jobs, uint32_t job_len, uint32_t* epoch) {
@@ -162,6 +168,8 @@ snappy_b200_status lane_parse_all(snappy_b200_ctx* c, const sb::JobParams& p) {
     }
     return SNAPPY_B200_OK;
 }
+
+snappy_b200_status ensure_pipe(snappy_b200_ctx* c, size_t n_chunks);
 
 // Stream / fragment-range compression with input and output on the device.
 snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst,
@@ -200,9 +208,33 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.out_stride = 0;
     p.offsets = (const unsigned long long*)c->offsets.p;
     const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
+    // Both exact engines at once (mode 0 only): the lane parser is bound by DRAM accesses, the pipelined
+    // parser by shared memory and issue slots, so they run side by side on disjoint fragment ranges.
+    const uint32_t n_pipe = (lane && mode == SNAPPY_B200_EXACT) ? hybrid_pipe_frags(n_frag) : 0u;
     CU(cudaEventRecord(c->evp0, c->stream));
-    if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
-    else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
+    if (lane) {
+        sb::JobParams pl = p;
+        pl.n_jobs = n_frag - n_pipe;                             // the lane parser takes the leading fragments
+        if (n_pipe) {
+            if (ensure_pipe(c, 1) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+            CU(cudaEventRecord(c->ev_start, c->stream));
+            CU(cudaStreamWaitEvent(c->s_parse[0], c->ev_start, 0));
+        }
+        if (lane_parse_all(c, pl) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+        if (n_pipe) {
+            const uint64_t j0 = pl.n_jobs;
+            sb::JobParams pp = p;
+            pp.in += j0 * p.in_stride; pp.n_total -= j0 * p.in_stride;
+            pp.seqs += j0 * sb::seq_stride(p.job_len); pp.nseq += j0; pp.sizes += j0;
+            pp.n_jobs = n_pipe;
+            CU(sb::launch_parse(pp, SNAPPY_B200_EXACT, c->s_parse[0], &c->launches));
+            CU(sb::launch_size(pp, c->s_parse[0], &c->launches));
+            CU(cudaEventRecord(c->ev_done, c->s_parse[0]));
+            CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));
+        }
+    } else {
+        CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
+    }
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));   // the lane parser adds up sizes as it goes

@@ -415,7 +415,7 @@ static int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 // tuning knobs: SNAPPY_B200_LANE_VAR = kVar bits of parse_lane.cuh, SNAPPY_B200_LANE_FPW = fragments per warp
-static int lane_var() { static const int v = env_int("SNAPPY_B200_LANE_VAR", 32); return v; }
+static int lane_var() { static const int v = env_int("SNAPPY_B200_LANE_VAR", 40); return v; }
 
 size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
     return (size_t)n_jobs * table_entries(job_len) * ((lane_var() & 8) ? 32u : 16u);
@@ -425,14 +425,15 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
                               unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
     static_assert(sizeof(lane::Entry) == kLaneEntryBytes, "entry size");
-    static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0);
+    static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0), wpc_env = env_int("SNAPPY_B200_LANE_WPC", 0);
     LaneTable t;
     t.base = reinterpret_cast<uint8_t*>(pool);
     t.stride = table_entries(p.job_len);
     t.epoch = epoch;
-    t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 8u;
-    const uint32_t grid = (p.n_jobs + t.fpw - 1) / t.fpw;
-#define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, kLaneThreads, 0, st>>>(p, t); break;
+    t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 4u;
+    const uint32_t wpc = wpc_env >= 1 && wpc_env <= kLaneMaxThreads / 32 ? (uint32_t)wpc_env : 2u;
+    const uint32_t per_cta = t.fpw * wpc, grid = (p.n_jobs + per_cta - 1) / per_cta;
+#define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, 32 * wpc, 0, st>>>(p, t); break;
     switch (lane_var()) {
         SB_LANE_CASE(0) SB_LANE_CASE(1) SB_LANE_CASE(2) SB_LANE_CASE(4) SB_LANE_CASE(6) SB_LANE_CASE(8)
         SB_LANE_CASE(10) SB_LANE_CASE(9) SB_LANE_CASE(32) SB_LANE_CASE(33) SB_LANE_CASE(34) SB_LANE_CASE(40)

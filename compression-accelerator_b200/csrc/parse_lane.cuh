@@ -290,13 +290,13 @@ struct LaneTable {
     uint32_t fpw;              // fragments (active lanes) per warp
 };
 
-constexpr int kLaneThreads = 32;
+constexpr int kLaneMaxThreads = 128;   // up to four warps per CTA (32 CTAs per SM would otherwise cap the warps)
 
 template <int kVar>
-__global__ void __launch_bounds__(kLaneThreads) parse_lane_kernel(JobParams p, LaneTable t) {
+__global__ void __launch_bounds__(kLaneMaxThreads) parse_lane_kernel(JobParams p, LaneTable t) {
     const uint32_t lane_id = threadIdx.x & 31u;
     if (lane_id >= t.fpw) return;
-    const uint32_t warp = blockIdx.x * (kLaneThreads / 32) + (threadIdx.x >> 5);
+    const uint32_t warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const uint32_t job = warp * t.fpw + lane_id;
     if (job >= p.n_jobs) return;
     const uint32_t len = job_len_of(p, job);
