@@ -84,11 +84,12 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def measured_traffic(mode):
-    """DRAM bytes per launch of the mode's dominant kernel from the committed ncu capture."""
+def measured_traffic(mode, what="kernel"):
+    """DRAM bytes (ncu dram__bytes_read.sum + dram__bytes_write.sum) per launch of the mode's dominant
+    kernel, or summed over all kernels of one step, from the committed ncu capture of this workload."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            t = json.load(f)[mode]
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            t = json.load(f)[mode][what]
         return t["dram_read_bytes"] + t["dram_write_bytes"]
     except Exception:
         return None
@@ -97,6 +98,29 @@ def measured_traffic(mode):
 def corpus_1gib():
     import corpus
     return corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), GIB)
+
+
+def base_config(mode, n):
+    """The keys both arms print (the driver compares the two lines' `config`)."""
+    return {"workload": WORKLOAD, "mode": mode, "bytes_per_gpu": n, "fragments_per_gpu": n // 65536}
+
+
+def reference_stream_sha256(host):
+    """sha256 + length of the stream the reference's Snappy makes of `host` (one call, one thread; outside
+    every timer).  The checker is oracle/_ref when present, else the port (bench.py may run oracle/ only as
+    the checker and as the CPU arm)."""
+    import hashlib
+    import oracle_lib
+    t0 = time.perf_counter()
+    comp = oracle_lib.checker().compress(host.tobytes())
+    h = hashlib.sha256(comp).hexdigest()
+    log("reference stream: %d bytes, sha256 %s.. (%.1f s)" % (len(comp), h[:12], time.perf_counter() - t0))
+    return h, len(comp)
+
+
+def device_sha256(t, n):
+    import hashlib
+    return hashlib.sha256(t[:n].cpu().numpy().tobytes()).hexdigest()
 
 
 def cpu_reference(host, threads, budget_s=12.0):
@@ -142,7 +166,7 @@ def run_reference(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "mode": "exact"},
+            "config": base_config("exact", host.size),
             "cpu_baseline": {"value": val, "unit": "GB/s", "cores": threads, "kind": kind,
                              "sample": "each step = first %d MiB of the workload on %d host threads" % (sample >> 20, threads)},
             "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -276,7 +300,145 @@ def config_rows(ctx, pkg, stream, torch, peak):
                        "round_trip": bool(torch.equal(back[:page * count], buf) and bool((lens == page).all()))}
         del buf, comp, back, sizes, lens
     out["pages_1m_x_4k"] = pages
+    try:
+        out["size_sweep"] = size_sweep(ctx, stream, torch, dev, peak)
+    except Exception as e:
+        out["size_sweep"] = {"error": repr(e)}
     return out
+
+
+SWEEP_NOMINAL_MHZ = 1965          # "cycles" of the CSV rows = device ns per buffer x this clock
+
+
+def size_sweep(ctx, stream, torch, dev, peak):
+    """The reference's own result set (benchmark/hw_results.csv, sw_results.csv: 12 sizes x random / real /
+    repeating, DataGenerator.scala:27,44-67) through the batch entry: each point's buffer replicated until
+    the call moves >= 1 GiB, device-resident, CUDA events.  One buffer of every point is compared with the
+    oracle (all replicas are the same bytes, and their sizes are checked equal).  Rows in the reference's
+    `type;length;cycles;compressed-length` form are also written to profiles/."""
+    import numpy as np
+    import corpus
+    import oracle_lib
+    chk = oracle_lib.checker()
+    rows, csv = {}, ["type;length;cycles;compressed-length"]
+    for kind in ("random", "real", "repeating"):
+        for n in corpus.SWEEP_SIZES:
+            data = corpus.benchmark_file(kind, n)
+            count = -(-GIB // n)
+            one = torch.from_numpy(np.frombuffer(data, dtype=np.uint8).copy()).to(dev)
+            buf = one.repeat(count)
+            comp, ostride, sizes = ctx.compress_batch_device(buf, n, n, count)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 2
+            e0.record(stream)
+            for _ in range(reps):
+                ctx.compress_batch_device(buf, n, n, count, dst=comp, sizes=sizes)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            want = chk.compress(data)
+            k = count // 2
+            got = bytes(comp[k * ostride:k * ostride + int(sizes[k].item())].cpu().numpy())
+            same = got == want and bool((sizes == len(want)).all())
+            ns = ms * 1e6 / count
+            rows["%s-%d" % (kind, n)] = {"buffers": count, "ms": ms, "value": n * count / ms / 1e6, "unit": "GB/s",
+                                         "ns_per_buffer": ns, "compressed_bytes": len(want),
+                                         "roofline_frac": (n + len(want)) * count / ms / 1e6 / peak,
+                                         "identical_to_reference": same}
+            csv.append("%s;%d;%d;%d" % (kind, n, round(ns * SWEEP_NOMINAL_MHZ / 1e3), len(want)))
+            del buf, comp, sizes, one
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_size_sweep.csv"), "w") as f:
+            f.write("\n".join(csv) + "\n")
+    except OSError:
+        pass
+    rows["csv_note"] = ("cycles = device ns per buffer (batch of >= 1 GiB) x %d MHz; rows also in "
+                        "profiles/r02_size_sweep.csv" % SWEEP_NOMINAL_MHZ)
+    return rows
+
+
+def host_copy_ceiling(torch, dev, pinned_in, pinned_out, n_in, n_out, world, dist, reps=3):
+    """What the box's PCIe / host memory allows with no kernel at all: H2D of the input and D2H of a
+    stream-sized buffer, concurrently on two streams, from the same pinned buffers, on all ranks at once."""
+    d_in = torch.empty(n_in, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(n_out, dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def once():
+        with torch.cuda.stream(s1):
+            d_in.copy_(pinned_in[:n_in], non_blocking=True)
+        with torch.cuda.stream(s2):
+            pinned_out[:n_out].copy_(d_out, non_blocking=True)
+    once()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        once()
+    torch.cuda.synchronize()
+    secs = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(secs, op=dist.ReduceOp.MAX)
+    return world * n_in * reps / float(secs.item()) / 1e9
+
+
+def bind_near_gpu(local):
+    """Keep this rank's host thread (and so its first-touch pinned pages) on the CPUs next to its GPU."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        allowed = sorted(set(cpus) & os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return "%d cpus near gpu %d" % (len(allowed), local)
+    except Exception as e:
+        return "not bound (%r)" % (e,)
+
+
+def sharded_stream_row(ctx, pkg, dev, torch, dist, rank, world, steps):
+    """SURVEY.md 8d config 5, second half: ONE 2 GiB stream whose fragments are sharded over the ranks
+    (strong scaling), payloads assembled on rank 0 by the peer-memory exchange; the root's stream is
+    compared with the reference Snappy's."""
+    import corpus
+    from compression_accelerator_b200 import multi
+    n2 = 2 * GIB
+    host2 = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n2)
+    ss = multi.PeerShardedStream(ctx, n2, dev)
+    shard = torch.from_numpy(host2[ss.lo:ss.hi]).to(dev)
+    want = reference_stream_sha256(host2) if rank == 0 else (None, None)
+    del host2
+    for _ in range(2):
+        k = ss.submit(shard)
+        ss.finish(k)
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        k = ss.submit(shard)
+        if k >= 1:
+            ss.finish(k - 1)
+    total, stream_t = ss.finish(k)
+    secs = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(secs, op=dist.ReduceOp.MAX)
+    same = None
+    if rank == 0:
+        same = total == want[1] and device_sha256(stream_t, total) == want[0]
+    ms = float(secs.item()) * 1e3 / steps
+    row = {"ms": ms, "value": n2 / ms / 1e6, "unit": "GB/s", "bytes": n2, "fragments_per_rank": (ss.hi - ss.lo) // 65536,
+           "stream_bytes": total, "identical_to_reference": same, "scaling": "strong",
+           "timing": "host clock around %d pipelined submits + the last finish, max over ranks" % steps}
+    dist.barrier()
+    if rank != 0:
+        ss.close()
+    dist.barrier()
+    if rank == 0:
+        ss.close()
+    return row
 
 
 def run_ours(args):
@@ -292,6 +454,7 @@ def run_ours(args):
         log("note: WORLD_SIZE=%d, --gpus=%d; using WORLD_SIZE" % (world, args.gpus))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    binding = bind_near_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     pkg = g.load_package()
@@ -300,6 +463,7 @@ def run_ours(args):
 
     host = corpus_1gib()
     n = host.size
+    ref_sha, ref_len = reference_stream_sha256(host) if rank == 0 else (None, None)
     pinned_in = torch.empty(n, dtype=torch.uint8).pin_memory()
     pinned_in.numpy()[:] = host
     src = torch.empty(n, dtype=torch.uint8, device=dev)
@@ -393,6 +557,31 @@ def run_ours(args):
     clk = clocks.stop() if rank == 0 else None
     comp_n = int(out_n.item())
 
+    # ---- the timed streams are the reference's, byte for byte (checked outside every timer) ----
+    verified = None
+    if exchange == "peer":
+        last = step_no[0] - 1
+        total, offs = peer.wait(last)
+        if rank == 0:
+            slot = peer.archive(last & 1)
+            ends = offs[1:] + [total]
+            ok = sum(1 for r in range(world)
+                     if ends[r] - offs[r] == ref_len and device_sha256(slot[offs[r]:ends[r]], ref_len) == ref_sha)
+            verified = {"headline_stream_equals_reference": ok == world, "archive_streams_equal_reference": ok,
+                        "checker": "sha256 of every rank's stream in the root's archive slot of the last timed step"}
+    elif rank == 0:
+        if world > 1:
+            offs = sharder.offsets
+            ends = offs[1:] + [sharder.total]
+            ok = sum(1 for r in range(world)
+                     if ends[r] - offs[r] == ref_len and device_sha256(sharder.archive[offs[r]:ends[r]], ref_len) == ref_sha)
+            verified = {"headline_stream_equals_reference": ok == world, "archive_streams_equal_reference": ok}
+        else:
+            verified = {"headline_stream_equals_reference": comp_n == ref_len and device_sha256(dst, comp_n) == ref_sha,
+                        "checker": "sha256 of the device stream of the last timed step vs the reference Snappy's stream"}
+    if world > 1:
+        dist.barrier()
+
     # ---- end to end through the host-pointer C-ABI entry, pinned host buffers -----------
     pinned_out = torch.empty(cap, dtype=torch.uint8).pin_memory()
     e2e_steps = max(2, min(args.steps, 5))
@@ -407,6 +596,11 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     assert got == comp_n, (got, comp_n)
+    e2e_same = None
+    if rank == 0:
+        import hashlib
+        e2e_same = hashlib.sha256(pinned_out[:got].numpy().tobytes()).hexdigest() == ref_sha
+    ceiling = host_copy_ceiling(torch, dev, pinned_in, pinned_out, n, comp_n, world, dist)
 
     # ---- the other parse mode, same workload, same two measurements (reported beside the headline) ----
     other = "fast" if args.mode == "exact" else "exact"
@@ -432,6 +626,12 @@ def run_ours(args):
         dist.all_reduce(e2e_o, op=dist.ReduceOp.MAX)
     mode_now[0] = args.mode
 
+    sharded = None
+    if world > 1 and exchange == "peer":
+        try:
+            sharded = sharded_stream_row(ctx, pkg, dev, torch, dist, rank, world, args.steps)
+        except Exception as e:
+            sharded = {"error": repr(e)}
     extra = cfg_rows = None
     if rank == 0 and world == 1:
         try:
@@ -457,24 +657,31 @@ def run_ours(args):
             "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "mode": args.mode, "bytes_per_gpu": n,
-                       "fragments_per_gpu": n // 65536, "compressed_bytes_per_gpu": comp_n,
-                       "ratio_out_in": comp_n / n,
+            "config": base_config(args.mode, n),
+            "config_detail": {"compressed_bytes_per_gpu": comp_n, "ratio_out_in": comp_n / n, "host_binding": binding,
                        "l2": "input (1 GiB) and staging are larger than the 126 MB L2; no flush needed",
                        "multi_gpu": ("single GPU" if world == 1 else
                                      "weak: 1 GiB per rank; sizes, offsets and payloads move to rank 0's archive by the "
                                      "library's kernels over NVLink peer memory (CUDA IPC), two slots, step k's payload "
                                      "moves while step k+1 is compressed" if exchange == "peer" else
                                      "weak: 1 GiB per rank; NCCL all_gather of sizes + payload send/recv to rank 0")},
-            "roofline": {"bound": "hbm", "kernel": "parse_pipe_kernel<true>" if args.mode == "exact" else "parse_fast_kernel",
+            "verified": verified,
+            "roofline": {"bound": "hbm", "kernel": "parse_lane_kernel<40>" if args.mode == "exact" else "parse_fast_kernel",
                          "achieved": ach, "peak": peak,
-                         "unit": "GB/s", "frac": ach / peak, "traffic": measured_traffic(args.mode), "peak_source": peak_src,
+                         "unit": "GB/s", "frac": ach / peak, "traffic": measured_traffic(args.mode),
+                         "traffic_step": measured_traffic(args.mode, "step"), "peak_source": peak_src,
+                         "frac_of_nominal_8000": ach / 8000.0,
+                         "step_frac": algo / ((pms + gms) * 1e-3) / 1e9 / peak,
                          "algorithmic_bytes": algo, "kernel_ms": pms, "scan_gather_ms": gms,
                          "kernel_share_of_step": pms / (pms + gms) if pms + gms else None},
             "cpu_baseline": cpu,
             "e2e": {"value": world * n * e2e_steps / float(e2e_s.item()) / 1e9, "unit": "GB/s",
                     "h2d_bytes_per_step": n, "d2h_bytes_per_step": comp_n + 8,
-                    "api": "snappy_b200_compress (host pointers, pinned)"},
+                    "api": "snappy_b200_compress (host pointers, pinned)", "stream_equals_reference": e2e_same,
+                    "host_copy_ceiling_GBps": ceiling,
+                    "ceiling_note": "plain concurrent cudaMemcpyAsync H2D(input) + D2H(stream) from the same pinned "
+                                    "buffers on all ranks, no kernels"},
+            "sharded_stream_2gib": sharded,
             "gpu_launches": launches, "clocks": clk,
             "other_mode": {"mode": other, "value": world * n * args.steps / (ms_o * 1e-3) / 1e9, "unit": "GB/s",
                            "e2e": world * n * e2e_steps / float(e2e_o.item()) / 1e9,

@@ -150,9 +150,14 @@ def varint32(n: int) -> bytes:
 
 
 def _addr(buf):
-    """Address of a bytes / bytearray / numpy array / ctypes buffer without copying."""
-    if isinstance(buf, (bytes, bytearray)):
-        return C.cast(C.c_char_p(bytes(buf)) if isinstance(buf, bytearray) else C.c_char_p(buf), C.c_void_p).value
+    """A ctypes argument for the bytes of a bytes / bytearray / numpy array / tensor / ctypes buffer, without
+    copying.  For a bytearray the result is a ctypes array SHARING its memory (the caller passes it straight
+    to the C call, which keeps it alive for the call's duration); for the others an integer address of memory
+    the caller's own reference keeps alive."""
+    if isinstance(buf, bytearray):
+        return (C.c_char * len(buf)).from_buffer(buf)
+    if isinstance(buf, bytes):
+        return C.cast(C.c_char_p(buf), C.c_void_p).value
     if hasattr(buf, "ctypes"):
         return buf.ctypes.data
     if hasattr(buf, "data_ptr"):
@@ -192,6 +197,35 @@ class Context:
     @property
     def last_kernel_ms(self) -> float:
         return lib().snappy_b200_last_kernel_ms(self._h)
+
+    # ---- ordering against torch's streams ------------------------------------------------
+    # The library works on its own non-blocking stream.  Every entry that takes torch tensors first makes
+    # that stream wait for torch's current stream (so a src still being produced by a torch op, or a dst
+    # torch has just allocated, is ready), tells the caching allocator the tensors are in use there, and
+    # afterwards makes torch's current stream wait for the library's work (so `out_n.item()`, slicing or
+    # freeing a result is ordered behind it without an explicit sync()).
+    def _ext(self):
+        import torch
+        if getattr(self, "_ext_stream", None) is None:
+            self._ext_stream = torch.cuda.ExternalStream(self.stream, device=torch.device("cuda", self.device))
+        return self._ext_stream
+
+    def _enter(self, *tensors):
+        import torch
+        cur = torch.cuda.current_stream(self.device)
+        ext = self._ext()
+        if cur.cuda_stream != ext.cuda_stream:
+            ext.wait_stream(cur)
+            for t in tensors:
+                if t is not None:
+                    t.record_stream(ext)
+
+    def _exit(self):
+        import torch
+        cur = torch.cuda.current_stream(self.device)
+        ext = self._ext()
+        if cur.cuda_stream != ext.cuda_stream:
+            cur.wait_stream(ext)
 
     def stage_ms(self, stage: int) -> float:
         """Device ms of stage 0 (parse kernel) / 1 (scan + gather) of the last device call."""
@@ -245,8 +279,10 @@ class Context:
         """Decode the n-byte raw stream in device tensor `src` into `dst`; asynchronous.  out_n (a
         1-element int64 device tensor) receives the decoded length, or -1 for a malformed stream.
         Streams of 128 KiB and more are decoded block-parallel when they are block structured."""
+        self._enter(src, dst, out_n)
         _check(lib().snappy_b200_uncompress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
                                                    out_n.data_ptr()))
+        self._exit()
         return dst, out_n
 
     def uncompress_batch_device(self, src, in_stride, sizes, count, out_stride, dst=None, out_lens=None):
@@ -257,8 +293,10 @@ class Context:
             dst = torch.empty(out_stride * count, dtype=torch.uint8, device=src.device)
         if out_lens is None:
             out_lens = torch.zeros(count, dtype=torch.int32, device=src.device)
+        self._enter(src, sizes, dst, out_lens)
         _check(lib().snappy_b200_uncompress_batch_device(self._h, src.data_ptr(), in_stride, sizes.data_ptr(),
                                                          count, dst.data_ptr(), out_stride, out_lens.data_ptr()))
+        self._exit()
         return dst, out_lens
 
     # ---- Snappy framing format (tests/snappy/framing_format.txt) ------------------------
@@ -290,16 +328,20 @@ class Context:
             dst = torch.empty(cap, dtype=torch.uint8, device=src.device)
         if out_n is None:
             out_n = torch.zeros(1, dtype=torch.int64, device=src.device)
+        self._enter(src, dst, out_n)
         _check(lib().snappy_b200_frame_compress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
                                                        out_n.data_ptr(), _MODES[mode]))
+        self._exit()
         return dst, out_n
 
     def frame_uncompress_device(self, src, n, dst):
         """Decode the n-byte framed stream in device tensor `src` into `dst`; synchronous (every
         chunk's CRC is checked).  Returns the number of bytes written."""
         got = C.c_size_t(0)
+        self._enter(src, dst)
         _check(lib().snappy_b200_frame_uncompress_device(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(),
                                                          C.byref(got)))
+        self._exit()
         return got.value
 
     def crc32c_chunks_device(self, src, chunk_len=65536, out=None):
@@ -309,7 +351,9 @@ class Context:
         chunks = (n + chunk_len - 1) // chunk_len
         if out is None:
             out = torch.zeros(max(chunks, 1), dtype=torch.int32, device=src.device)
+        self._enter(src, out)
         _check(lib().snappy_b200_crc32c_chunks_device(self._h, src.data_ptr(), n, chunk_len, out.data_ptr()))
+        self._exit()
         return out[:chunks]
 
     # ---- device tensors (torch uint8, on this context's device) -------------------------
@@ -326,7 +370,9 @@ class Context:
         if out_n is None:
             out_n = torch.zeros(1, dtype=torch.int64, device=src.device)
         fn = lib().snappy_b200_compress_device if header else lib().snappy_b200_compress_fragments_device
+        self._enter(src, dst, out_n)
         _check(fn(self._h, src.data_ptr(), n, dst.data_ptr(), dst.numel(), out_n.data_ptr(), _MODES[mode]))
+        self._exit()
         return dst, out_n
 
     def compress_batch_device(self, src, length, stride, count, dst=None, sizes=None, mode="exact"):
@@ -336,9 +382,11 @@ class Context:
             dst = torch.empty(ostride * count, dtype=torch.uint8, device=src.device)
         if sizes is None:
             sizes = torch.zeros(count, dtype=torch.int32, device=src.device)
+        self._enter(src, dst, sizes)
         _check(lib().snappy_b200_compress_batch_device(self._h, src.data_ptr(), length, stride, count,
                                                        dst.data_ptr(), ostride, sizes.data_ptr(),
                                                        _MODES[mode]))
+        self._exit()
         return dst, ostride, sizes
 
 

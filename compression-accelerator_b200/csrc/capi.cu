@@ -71,6 +71,8 @@ struct snappy_b200_ctx {
     uint32_t lane_epoch = 0;                   // epoch of the pool's most recent launch (0 = pool all-empty)
     unsigned long long* d_total = nullptr;     // device
     unsigned long long* h_total = nullptr;     // pinned
+    unsigned int* h_err = nullptr;             // pinned + mapped: a parser watchdog stores 1 (surfaces as CUDA_ERROR)
+    unsigned int* h_err_dev = nullptr;         // its device alias
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t evp0 = nullptr, evp1 = nullptr, evp2 = nullptr;   // parse start / parse end / compact end
     bool staged = false;
@@ -103,6 +105,16 @@ snappy_b200_status bind(snappy_b200_ctx* c) {
 
 thread_local snappy_b200_ctx* g_default_ctx = nullptr;
 
+// After a synchronisation point: did a parser watchdog give up on a fragment?  (Its output is then a well
+// formed stream, but not the reference's bytes, so the call fails instead of returning it.)
+snappy_b200_status watchdog_status(snappy_b200_ctx* c) {
+    if (c->h_err && *(volatile unsigned int*)c->h_err) {
+        *(volatile unsigned int*)c->h_err = 0;
+        return fail(SNAPPY_B200_CUDA_ERROR, "parser watchdog: a fragment's pipeline stalled (result discarded)");
+    }
+    return SNAPPY_B200_OK;
+}
+
 snappy_b200_status default_ctx(snappy_b200_ctx** out) {
     if (!g_default_ctx) {
         snappy_b200_status st = snappy_b200_create(&g_default_ctx, 0);
@@ -116,11 +128,14 @@ snappy_b200_status default_ctx(snappy_b200_ctx** out) {
 // mode 0 (SNAPPY_B200_EXACT) picks by shape: the lane parser (one thread per fragment, all fragments in
 // flight, parse_lane.cuh) when the call has enough fragments to hide DRAM latency behind their number,
 // the pipelined parser (one CTA per fragment, parse_pipe.cuh) otherwise.  Modes 5 / 6 force one or the
-// other (tests, A/B runs); both produce the reference's bytes.
+// other (tests, A/B runs); both produce the reference's bytes.  Measured crossover on text (ms per
+// parse, pipelined vs lane): 512 MiB 15.5 vs 18.5, 1 GiB 31.3 vs 22.4, 2 GiB 62 vs 40.7.  Running both
+// side by side on disjoint fragment ranges was measured and lost (22.1 ms per GiB: the pipelined CTAs
+// need the maximum shared-memory carve-out, which leaves the lane parser 28 KB of L1).
 constexpr int kModeLane = 5, kModePipe = 6;
 constexpr size_t kLanePoolMaxBytes = 20ull << 30;
 inline uint32_t lane_min_frags() {
-    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 3072u; }();
+    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 10240u; }();
     return v;
 }
 inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
@@ -129,13 +144,6 @@ inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
            sb::lane_pool_bytes(n_jobs, job_len) <= kLanePoolMaxBytes;
 }
 inline int kernel_mode(int mode) { return mode == kModePipe ? (int)SNAPPY_B200_EXACT : mode; }
-// Fragments of a lane-parsed stream that go to the pipelined parser instead (it runs beside the lane
-// parser; the split makes both finish together: SNAPPY_B200_HYBRID_PIPE_PCT = its share in percent).
-inline uint32_t hybrid_pipe_frags(uint32_t n_frag) {
-    static const int pct = [] { const char* e = getenv("SNAPPY_B200_HYBRID_PIPE_PCT"); return e ? atoi(e) : 45; }();
-    return pct <= 0 ? 0u : (uint32_t)((uint64_t)n_frag * (uint64_t)(pct > 100 ? 100 : pct) / 100u);
-}
-
 // Reserve the pool for `n_jobs` tables and open a new epoch (stream-ordered on c->stream).
 snappy_b200_status lane_begin(snappy_b200_ctx* c, uint64_t n_jobs, uint32_t job_len, uint32_t* epoch) {
     const size_t need = sb::lane_pool_bytes(n_jobs, job_len);
@@ -168,8 +176,6 @@ snappy_b200_status lane_parse_all(snappy_b200_ctx* c, const sb::JobParams& p) {
     }
     return SNAPPY_B200_OK;
 }
-
-snappy_b200_status ensure_pipe(snappy_b200_ctx* c, size_t n_chunks);
 
 // Stream / fragment-range compression with input and output on the device.
 snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n, void* d_dst,
@@ -207,34 +213,11 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.out = (uint8_t*)d_dst + (framed ? 8 : 0);
     p.out_stride = 0;
     p.offsets = (const unsigned long long*)c->offsets.p;
+    p.err = c->h_err_dev;
     const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
-    // Both exact engines at once (mode 0 only): the lane parser is bound by DRAM accesses, the pipelined
-    // parser by shared memory and issue slots, so they run side by side on disjoint fragment ranges.
-    const uint32_t n_pipe = (lane && mode == SNAPPY_B200_EXACT) ? hybrid_pipe_frags(n_frag) : 0u;
     CU(cudaEventRecord(c->evp0, c->stream));
-    if (lane) {
-        sb::JobParams pl = p;
-        pl.n_jobs = n_frag - n_pipe;                             // the lane parser takes the leading fragments
-        if (n_pipe) {
-            if (ensure_pipe(c, 1) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-            CU(cudaEventRecord(c->ev_start, c->stream));
-            CU(cudaStreamWaitEvent(c->s_parse[0], c->ev_start, 0));
-        }
-        if (lane_parse_all(c, pl) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-        if (n_pipe) {
-            const uint64_t j0 = pl.n_jobs;
-            sb::JobParams pp = p;
-            pp.in += j0 * p.in_stride; pp.n_total -= j0 * p.in_stride;
-            pp.seqs += j0 * sb::seq_stride(p.job_len); pp.nseq += j0; pp.sizes += j0;
-            pp.n_jobs = n_pipe;
-            CU(sb::launch_parse(pp, SNAPPY_B200_EXACT, c->s_parse[0], &c->launches));
-            CU(sb::launch_size(pp, c->s_parse[0], &c->launches));
-            CU(cudaEventRecord(c->ev_done, c->s_parse[0]));
-            CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));
-        }
-    } else {
-        CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
-    }
+    if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
+    else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));   // the lane parser adds up sizes as it goes
@@ -355,6 +338,7 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         p.out = d_out;
         p.out_stride = 0;
         p.offsets = (const unsigned long long*)c->offsets.p + f0;
+        p.err = c->h_err_dev;
         cudaStream_t ps = c->s_parse[k % n_ps];
         CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
         if (lane)
@@ -388,6 +372,7 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaStreamSynchronize(c->s_d2h));
     if (st != SNAPPY_B200_OK) return st;
+    if (watchdog_status(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     *out_n = done;
     return SNAPPY_B200_OK;
@@ -445,6 +430,9 @@ snappy_b200_status snappy_b200_create(snappy_b200_ctx** out, int device) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaMalloc(&c->d_total, sizeof(unsigned long long)));
     CU(cudaMallocHost(&c->h_total, sizeof(unsigned long long)));
+    CU(cudaHostAlloc((void**)&c->h_err, sizeof(unsigned int), cudaHostAllocMapped));
+    *c->h_err = 0;
+    CU(cudaHostGetDevicePointer((void**)&c->h_err_dev, c->h_err, 0));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
     CU(cudaEventCreate(&c->evp0));
@@ -463,6 +451,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     c->crcs.release(); c->frame_ix.release(); c->frame_res.release(); c->raw_ix.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
+    if (c->h_err) cudaFreeHost(c->h_err);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->evp0) cudaEventDestroy(c->evp0);
@@ -505,7 +494,7 @@ snappy_b200_status snappy_b200_sync(snappy_b200_ctx* c) {
     if (!c) return fail(SNAPPY_B200_INVALID_INPUT, "null ctx");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(cudaStreamSynchronize(c->stream));
-    return SNAPPY_B200_OK;
+    return watchdog_status(c);
 }
 
 void* snappy_b200_host_alloc(size_t n) {
@@ -559,6 +548,7 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.out = (uint8_t*)d_dst;
     p.out_stride = out_stride;
     p.offsets = nullptr;
+    p.err = c->h_err_dev;
     const bool lane = lane_chosen(mode, count, (uint32_t)len);
     CU(cudaEventRecord(c->evp0, c->stream));
     if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
@@ -596,6 +586,7 @@ snappy_b200_status snappy_b200_compress(snappy_b200_ctx* c, const void* src, siz
     if (total > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "stream larger than dst_cap");
     CU(cudaMemcpyAsync(dst, c->d_out.p, total, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    if (watchdog_status(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     *out_n = total;
     return SNAPPY_B200_OK;
@@ -622,6 +613,7 @@ snappy_b200_status snappy_b200_compress_batch(snappy_b200_ctx* c, const void* sr
     CU(cudaMemcpyAsync(sizes, c->sizes.p, count * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(dst, c->d_out.p, out_bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    if (watchdog_status(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     return SNAPPY_B200_OK;
 }

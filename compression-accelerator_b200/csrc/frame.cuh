@@ -254,15 +254,16 @@ __global__ void frame_walk_kernel(const uint8_t* __restrict__ src, uint64_t n, F
             if (type == 0x00) {                                              // varint32 preamble of the chunk's stream
                 ulen = 0;
                 uint32_t shift = 0, i = 0;
+                bool bad_varint = false;             // local: err may already be 2 (index full, keep counting)
                 for (;; ++i) {
-                    if (i >= plen || shift > 28) { err = 1; break; }
+                    if (i >= plen || shift > 28) { bad_varint = true; break; }
                     const uint32_t b = src[pay + i];
-                    if (shift == 28 && (b & 0x7fu) > 15u) { err = 1; break; }
+                    if (shift == 28 && (b & 0x7fu) > 15u) { bad_varint = true; break; }
                     ulen |= (b & 0x7fu) << shift;
                     if (b < 128) break;
                     shift += 7;
                 }
-                if (err) break;
+                if (bad_varint) { err = 1; break; }
             }
             if (ulen > kFrameChunk) { err = 1; break; }                      // :88-91, :104-106
             if (cnt < max_records) {

@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(32 * (1 + PipeCfg<kGlobal>::P)) parse_pipe_ker
             for (uint32_t i = len + tid; i < padded; i += NT) s_in[i] = 0;
         }
         if (tid < R) ps->ready[tid] = 0;
-        if (tid == 0) { ps->cur_win = 0; mbar_init(&ps->bar, 1); }
+        if (tid == 0) { ps->cur_win = 0; ps->err = p.err; mbar_init(&ps->bar, 1); }
     }
     __syncthreads();
     if (bulk) mbar_wait(bar, 0);
@@ -356,6 +356,10 @@ cudaError_t read_stats(unsigned long long* out16, bool reset) {
 #endif
 }
 
+// kVar values of parse_lane.cuh that are compiled in (40 is the product default; the others are kept for
+// A/B runs through SNAPPY_B200_LANE_VAR)
+#define SB_LANE_VARIANTS(X) X(0) X(2) X(32) X(34) X(40) X(42)
+
 cudaError_t kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)parse_smem_bytes(kBlock));
@@ -435,9 +439,7 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
     const uint32_t per_cta = t.fpw * wpc, grid = (p.n_jobs + per_cta - 1) / per_cta;
 #define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, 32 * wpc, 0, st>>>(p, t); break;
     switch (lane_var()) {
-        SB_LANE_CASE(0) SB_LANE_CASE(1) SB_LANE_CASE(2) SB_LANE_CASE(4) SB_LANE_CASE(6) SB_LANE_CASE(8)
-        SB_LANE_CASE(10) SB_LANE_CASE(9) SB_LANE_CASE(32) SB_LANE_CASE(33) SB_LANE_CASE(34) SB_LANE_CASE(40)
-        SB_LANE_CASE(41) SB_LANE_CASE(42)
+        SB_LANE_VARIANTS(SB_LANE_CASE)
         default: return cudaErrorInvalidValue;
     }
 #undef SB_LANE_CASE

@@ -43,6 +43,7 @@ struct JobParams {
     uint8_t* out;
     uint64_t out_stride;
     const unsigned long long* offsets;
+    unsigned int* err = nullptr;   // the context's error word (mapped host memory): a parser watchdog stores 1 here
 };
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned long long* launches);
@@ -128,10 +129,10 @@ struct PeerTable {
     PeerMailbox* box[kPeerMaxWorld];                         // box[r] = rank r's mailbox as mapped here
 };
 
-cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, unsigned long long step,
+cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, uint32_t root, unsigned long long step,
                              unsigned long long base, const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
                              unsigned long long slot_bytes, unsigned long long* d_offset,
-                             unsigned long long* d_error, cudaStream_t st, cudaEvent_t copied,
+                             cudaStream_t st, cudaEvent_t copied,
                              unsigned long long* launches);
 cudaError_t launch_peer_wait(PeerMailbox* mine, uint32_t world, unsigned long long step, cudaStream_t st,
                              unsigned long long* launches);

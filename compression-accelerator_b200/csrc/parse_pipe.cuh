@@ -62,6 +62,7 @@ struct alignas(16) PipeShared {
     uint4 rec[R][32];                    // x = h | Tspec<<16, y = nx | ek<<16, z = ph (lanes with my hash), w = chain summary (lanes taken when the fast path enters at this lane)
     volatile uint32_t ready[R];          // window index + 1 whose record is complete
     volatile uint32_t cur_win;           // resolver's current window, kDone when the parse ended
+    unsigned int* err;                   // the context's error word (mapped host memory) or null: watchdogs raise it
     uint64_t bar;                        // mbarrier (count 1): the resolver arrives whenever cur_win moves
 };
 
@@ -148,7 +149,10 @@ __device__ __forceinline__ void pipe_producer(const Src& src, const uint16_t* ta
 #if SB_PIPE_SLEEP > 0
             else __nanosleep(SB_PIPE_SLEEP);                 // try_wait times out quickly: do not burn issue slots
 #endif
-            if (++idle > (1u << 24)) __trap();               // watchdog: never hang the GPU
+            if (++idle > (1u << 24)) {                       // watchdog: never hang the GPU, never poison the context
+                if (lane == 0 && ps->err) *(volatile unsigned int*)ps->err = 1u;
+                return;                                      // the resolver's own watchdog ends the fragment
+            }
             continue;
         }
         idle = 0;
@@ -220,8 +224,13 @@ struct PipeResolver {
 #ifdef SNAPPY_B200_STATS
             const long long t0 = clock64();
 #endif
+            bool stuck = false;
             for (uint32_t spins = 0; ps->ready[si] != win + 1; ++spins)
-                if (spins > (1u << 24)) __trap();            // watchdog: never hang the GPU
+                if (spins > (1u << 24)) { stuck = true; break; }
+            if (__any_sync(kFull, stuck)) {                  // watchdog: raise the context's error word and end the
+                if (lane == 0 && ps->err) *(volatile unsigned int*)ps->err = 1u;   // fragment (the caller emits the
+                return;                                      // rest as one literal, so the lists stay well formed)
+            }
 #ifdef SNAPPY_B200_STATS
             st_wait += clock64() - t0; ++st_win;
 #endif

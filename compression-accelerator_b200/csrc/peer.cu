@@ -110,9 +110,9 @@ snappy_b200_status snappy_b200_peer_gather(snappy_b200_peer* p, const void* d_pa
     cudaStream_t cs = (cudaStream_t)snappy_b200_stream(p->ctx);
     PCU(cudaEventRecord(p->ev_in, cs));                      // behind the compress kernels queued so far
     PCU(cudaStreamWaitEvent(p->xs, p->ev_in, 0));
-    PCU(sb::launch_peer_step(p->table, p->rank, p->world, step, base, (const uint8_t*)d_payload, d_size,
+    PCU(sb::launch_peer_step(p->table, p->rank, p->world, p->root, step, base, (const uint8_t*)d_payload, d_size,
                              p->archive + (step & 1) * p->slot_bytes, p->slot_bytes, p->d_offset + (step & 1),
-                             &p->box->error, p->xs, p->ev_copied[step & 1], &p->launches));
+                             p->xs, p->ev_copied[step & 1], &p->launches));
     return SNAPPY_B200_OK;
 }
 

@@ -33,7 +33,14 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     return v;
 }
 
-__global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t, uint32_t rank, uint32_t world,
+// Errors are raised in the ROOT's mailbox as well as in the rank's own: the root is where
+// snappy_b200_peer_result looks, so a rank that timed out or overflowed its slot fails the step for all.
+__device__ __forceinline__ void peer_raise(const PeerTable& t, uint32_t rank, uint32_t root, unsigned long long code) {
+    t.box[rank]->error = code;
+    if (root != rank) st_release_sys(&t.box[root]->error, code);
+}
+
+__global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t, uint32_t rank, uint32_t world, uint32_t root,
                                                                      unsigned long long step, unsigned long long base,
                                                                      const unsigned long long* __restrict__ d_size,
                                                                      unsigned long long* d_offset) {
@@ -52,18 +59,21 @@ __global__ void __launch_bounds__(kPeerMaxWorld) peer_publish_kernel(PeerTable t
     const unsigned long long tag = (step + 1) << kPeerSizeBits;
     if (tid < world) st_release_sys(&t.box[tid]->sizes[step & 1][rank], tag | size);
     unsigned long long below = 0;
-    if (tid < rank) {
+    // Sizes of the ranks below me (my offset), and the ROOT's size word whatever its rank: the root
+    // publishes step k only after its host is done with the slot's previous content (step k-2), so no
+    // payload of step k reaches the slot before that -- also when the root is not rank 0.
+    if (tid < rank || (tid == root && tid != rank && tid < world)) {
         unsigned long long v;
         while (((v = ld_acquire_sys(&mine->sizes[step & 1][tid])) >> kPeerSizeBits) != step + 1)
             if (clock64() - t0 > 2 * kPeerSpinCycles) { bad = 1; break; }
-        below = v & ((1ull << kPeerSizeBits) - 1);
+        if (tid < rank) below = v & ((1ull << kPeerSizeBits) - 1);
     }
     part[tid] = below;
     __syncthreads();
     if (tid == 0) {
         unsigned long long off = base;                       // bytes the root keeps in front (a stream header)
         for (uint32_t r = 0; r < rank; ++r) off += part[r];
-        if (bad) { off = ~0ull; mine->error = 1; }
+        if (bad) { off = ~0ull; peer_raise(t, rank, root, 1); }
         *d_offset = off;
     }
 }
@@ -110,14 +120,14 @@ __device__ __forceinline__ void peer_tile_copy(uint8_t* __restrict__ d, const ui
     if (done + tid < n) d[done + tid] = s[done + tid];
 }
 
-__global__ void __launch_bounds__(256) peer_copy_kernel(const uint8_t* __restrict__ src,
+__global__ void __launch_bounds__(256) peer_copy_kernel(PeerTable t, uint32_t rank, uint32_t root,
+                                                        const uint8_t* __restrict__ src,
                                                         const unsigned long long* __restrict__ d_size,
                                                         uint8_t* archive, unsigned long long archive_cap,
-                                                        const unsigned long long* __restrict__ d_offset,
-                                                        unsigned long long* d_error, uint32_t tile) {
+                                                        const unsigned long long* __restrict__ d_offset, uint32_t tile) {
     const unsigned long long n = *d_size, off = *d_offset;
     if (off == ~0ull) return;
-    if (off + n > archive_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) *d_error = 2; return; }
+    if (off + n > archive_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) peer_raise(t, rank, root, 2); return; }
     const unsigned long long tiles = (n + tile - 1) / tile;
     for (unsigned long long k = blockIdx.x; k < tiles; k += gridDim.x) {
         const unsigned long long lo = k * tile;
@@ -141,18 +151,18 @@ __global__ void __launch_bounds__(kPeerMaxWorld) peer_wait_kernel(PeerMailbox* m
 }
 
 
-cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, unsigned long long step,
+cudaError_t launch_peer_step(const PeerTable& t, uint32_t rank, uint32_t world, uint32_t root, unsigned long long step,
                              unsigned long long base, const uint8_t* payload, const unsigned long long* d_size, uint8_t* archive_slot,
                              unsigned long long slot_bytes, unsigned long long* d_offset,
-                             unsigned long long* d_error, cudaStream_t st, cudaEvent_t copied,
+                             cudaStream_t st, cudaEvent_t copied,
                              unsigned long long* launches) {
-    peer_publish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step, base, d_size, d_offset);
+    peer_publish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, root, step, base, d_size, d_offset);
     // Few CTAs on purpose: 32 reach ~500 GB/s over NVLink when alone, and remote stores back up the
     // load/store path of the SM they run on, which slows the parser's CTAs sharing it (2 GPUs, ms per
     // step: 296 CTAs 33.70, 32 CTAs 33.36, 12 CTAs 33.61).  SNAPPY_B200_PEER_CTAS / _TILE_KB for A/B.
     static const uint32_t ctas = [] { const char* e = getenv("SNAPPY_B200_PEER_CTAS"); return e ? (uint32_t)atoi(e) : 32u; }();
     static const uint32_t tile = [] { const char* e = getenv("SNAPPY_B200_PEER_TILE_KB"); return (e ? (uint32_t)atoi(e) : 256u) << 10; }();
-    peer_copy_kernel<<<ctas, 256, 0, st>>>(payload, d_size, archive_slot, slot_bytes, d_offset, d_error, tile);
+    peer_copy_kernel<<<ctas, 256, 0, st>>>(t, rank, root, payload, d_size, archive_slot, slot_bytes, d_offset, tile);
     cudaError_t e = cudaEventRecord(copied, st);
     if (e != cudaSuccess) return e;
     peer_finish_kernel<<<1, kPeerMaxWorld, 0, st>>>(t, rank, world, step);

@@ -89,8 +89,19 @@ static void accept(b200_rocc* d) {
         d->resp_valid = 1;
         d->busy_cycles += (uint64_t)(snappy_b200_last_kernel_ms(d->ctx) * 1e6f);   // 1 cycle = 1 ns
     } else if (d->funct == B200_ROCC_UNCOMPRESS) {     // :385-388 (a stub in the reference hardware)
-        d->resp_data = snappy_b200_rocc_uncompress((char*)d->mem + d->rs1, (int)d->length,
-                                                   (char*)d->mem + d->rs2);
+        // Same operand checks as COMPRESS: source, length, destination and the length the stream's own
+        // preamble announces must all lie inside the device's memory (a poked address or a crafted stream
+        // must not reach host memory outside it).  Non-zero = failure (tests/compression.c:32-39).
+        const uint64_t src = d->rs1, dst = d->rs2, n = d->length;
+        uint64_t result = 1;
+        size_t ulen = 0, out_n = 0;
+        if (src <= d->mem_bytes && n >= 1 && n <= d->mem_bytes - src && dst <= d->mem_bytes &&
+            snappy_b200_uncompressed_length(d->mem + src, (size_t)n, &ulen) == SNAPPY_B200_OK &&
+            ulen <= d->mem_bytes - dst &&
+            snappy_b200_uncompress(d->ctx, d->mem + src, (size_t)n, d->mem + dst, d->mem_bytes - dst, &out_n) ==
+                SNAPPY_B200_OK)
+            result = 0;
+        d->resp_data = result;
         d->resp_valid = 1;
     }
 }

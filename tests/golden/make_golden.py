@@ -100,6 +100,21 @@ def main():
             key = ("repeat" if kind == "repeating" else kind, n)
             if key in csv_len:
                 man["sw_results_csv"]["%s-%d" % (kind, n)] = csv_len[key]
+    # the reference's own corrupted streams (snappy_unittest.cc:585-600 CorruptedTest: each must be refused
+    # by IsValidCompressedBuffer and Uncompress, and must not announce a crazy length)
+    man["bad"] = {}
+    for i in (1, 2, 3):
+        rel = "tests/snappy/testdata/baddata%d.snappy" % i
+        data = open(os.path.join(REF, rel), "rb").read()
+        store("baddata%d.snappy" % i, data)
+        try:
+            ulen = ref.uncompressed_length(data)
+        except ValueError:
+            ulen = None
+        assert not ref.is_valid(data)
+        man["bad"]["baddata%d.snappy" % i] = {"source": rel, "n": len(data), "announced_length": ulen,
+                                              "reference_is_valid": False,
+                                              "input_sha256": hashlib.sha256(data).hexdigest()}
     with open(os.path.join(HERE, "manifest.json"), "w") as f:
         json.dump(man, f, indent=1, sort_keys=True)
     print("wrote", len(man["files"]), "files,", len(man["kats"]), "kats,", len(man["sweep"]), "sweep points")

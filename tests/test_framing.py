@@ -159,3 +159,66 @@ def test_frame_device_entries_large(ctx):
     first_len = 4 + int.from_bytes(bytes(dst[11:14].cpu().numpy()), "little")
     want = oracle_lib.frame_compress(host[:65536].tobytes())
     assert bytes(dst[:10 + first_len].cpu().numpy()) == want
+
+
+# ---- a pin from OUTSIDE the restatement --------------------------------------------------------
+# Derived by hand from the specification text alone (tests/snappy/framing_format.txt) and one published
+# constant, the CRC-32C check value of the nine ASCII digits "123456789" = 0xE3069283 (the catalogued
+# check of CRC-32C/iSCSI, the algorithm RFC 3720 12.1 defines and the specification points at, :43-44):
+#   mask (:46-54):  x >> 15 = 0x0001C60D;  x << 17 = 0x25060000;  or = 0x2507C60D;  + 0xA282EAD8 = 0xC78AB0E5
+#   stored little-endian (:58): e5 b0 8a c7
+#   stream identifier (:68-75): ff 06 00 00 73 4e 61 50 70 59
+#   uncompressed chunk (:94-106): type 01, length = 4 (CRC) + 9 = 0x00000d LE -> 01 0d 00 00, CRC, data
+#   compressed chunk (:80-91): type 00, body = the data's own Snappy stream = varint(9) 09, literal tag
+#     (9-1)<<2 = 20 (format_description.txt:56-64), nine bytes -> 11 bytes, length 4 + 11 = 0x00000f
+HAND_CRC = "e5b08ac7"
+HAND_UNCOMPRESSED = "ff060000734e61507059" + "010d0000" + HAND_CRC + "313233343536373839"
+HAND_COMPRESSED = "ff060000734e61507059" + "000f0000" + HAND_CRC + "0920" + "313233343536373839"
+
+
+def test_hand_derived_vector_pins_the_restatement():
+    """The CPU restatement (the checker of the GPU framing tests) against the hand-derived bytes."""
+    assert oracle_lib.port().crc32c(b"123456789") == 0xE3069283
+    assert oracle_lib.port().crc32c_masked(b"123456789").to_bytes(4, "little").hex() == HAND_CRC
+    assert oracle_lib.frame_compress(b"123456789").hex() == HAND_COMPRESSED
+    assert oracle_lib.frame_uncompress(bytes.fromhex(HAND_UNCOMPRESSED)) == b"123456789"
+    assert oracle_lib.frame_uncompress(bytes.fromhex(HAND_COMPRESSED)) == b"123456789"
+
+
+@pytest.mark.gpu
+def test_hand_derived_vector_on_the_gpu(ctx):
+    """Writer emits exactly the hand-derived compressed-chunk stream; reader accepts both chunk forms."""
+    assert ctx.frame_compress(b"123456789").hex() == HAND_COMPRESSED
+    assert ctx.frame_uncompress(bytes.fromhex(HAND_UNCOMPRESSED)) == b"123456789"
+    assert ctx.frame_uncompress(bytes.fromhex(HAND_COMPRESSED)) == b"123456789"
+    x = bytearray.fromhex(HAND_UNCOMPRESSED)
+    x[14] ^= 1                                            # a CRC bit: must be refused
+    with pytest.raises(Exception):
+        ctx.frame_uncompress(bytes(x))
+
+
+@pytest.mark.gpu
+def test_frame_reader_many_small_chunks(ctx):
+    """More chunks than the reader's first index guess (2 * (dst_cap >> 16) + 1024): the walk must keep
+    counting after the index is full, and the second pass decodes the stream (frame.cuh)."""
+    p = oracle_lib.port()
+    text = corpus.fixture("alice29.txt")
+    parts, s = [], bytearray(oracle_lib.STREAM_ID)
+    for i in range(3000):
+        piece = text[i * 40:i * 40 + 40]
+        body = p.compress(piece)
+        s += bytes([0x00]) + (4 + len(body)).to_bytes(3, "little") + p.crc32c_masked(piece).to_bytes(4, "little") + body
+        parts.append(piece)
+    want = b"".join(parts)
+    assert oracle_lib.frame_uncompress(bytes(s)) == want
+    assert ctx.frame_uncompress(bytes(s)) == want
+
+
+@pytest.mark.gpu
+def test_bytearray_input(ctx, oracle):
+    """bytearray arguments are passed by address (no temporary copy may be freed under the C call)."""
+    data = bytearray(corpus.fixture("fox-in-socks.txt"))
+    framed = ctx.frame_compress(data)
+    assert framed == oracle_lib.frame_compress(bytes(data), oracle.compress)
+    assert ctx.frame_uncompress(bytearray(framed)) == bytes(data)
+    assert ctx.compress(data) == oracle.compress(bytes(data))

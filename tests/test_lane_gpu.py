@@ -89,9 +89,9 @@ def test_lane_host_entry_chunk_pipeline(ctx, oracle):
     assert comp == oracle.compress(data)
 
 
-def test_large_stream_whole_bytes(ctx, oracle):
-    """256 MiB of concatenated MTG text through the default exact mode (which picks the lane parser at
-    this size): the WHOLE stream equals the reference's, byte for byte."""
+def test_large_stream_every_exact_engine(ctx, oracle):
+    """256 MiB of concatenated MTG text through the default exact mode, the lane parser and the pipelined
+    parser: each WHOLE stream equals the reference's, byte for byte."""
     import torch
     n = 256 << 20
     host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)

@@ -272,3 +272,86 @@ def test_large_stream_mixed_content(ctx, oracle):
     for comp in (oracle.compress(data), ctx.compress(data, mode="fast")):
         assert len(comp) >= 128 << 10
         assert ctx.uncompress(comp) == data
+
+
+@pytest.mark.parametrize("name", sorted(MAN.get("bad", {})))
+def test_reference_corrupted_files_refused(ctx, pkg, name):
+    """tests/snappy/testdata/baddata{1,2,3}.snappy (snappy_unittest.cc:585-600): the reference refuses them
+    (IsValidCompressedBuffer / Uncompress false) and so must every decode path here: the host entry, the
+    device entry and the batch entry (one warp per stream, a good stream beside the bad one)."""
+    import torch
+    data = corpus.fixture(name)
+    ent = MAN["bad"][name]
+    assert len(data) == ent["n"]
+    with pytest.raises(pkg.SnappyB200Error) as ei:
+        ctx.uncompress(data)
+    assert ei.value.status == 1                                     # SNAPPY_B200_INVALID_INPUT
+    # device entry: out_n = -1 (all ones)
+    src = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+    dst = torch.zeros(ent["announced_length"] + 64, dtype=torch.uint8, device="cuda")
+    got = torch.zeros(1, dtype=torch.int64, device="cuda")
+    ctx.uncompress_device(src, len(data), dst, got)
+    ctx.sync()
+    assert int(got.item()) == -1
+    # batch entry (one warp per stream; a good stream beside it still decodes)
+    good = ctx.compress(b"neighbour " * 50)
+    stride = max(len(data), len(good)) + 16
+    buf = torch.zeros(2 * stride, dtype=torch.uint8, device="cuda")
+    buf[:len(data)] = src
+    buf[stride:stride + len(good)] = torch.frombuffer(bytearray(good), dtype=torch.uint8).cuda()
+    sizes = torch.tensor([len(data), len(good)], dtype=torch.int32, device="cuda")
+    out, lens = ctx.uncompress_batch_device(buf, stride, sizes, 2, ent["announced_length"] + 64)
+    ctx.sync()
+    assert int(lens[0].item()) == -1 and int(lens[1].item()) == 500
+
+
+def test_reference_zero_offset_and_four_byte_offset(ctx, pkg):
+    """snappy_unittest.cc:945-959 (copy with offset 0 must fail) and :732-764 (a hand-emitted copy with a
+    4-byte offset must decode)."""
+    for s in (b"\x40\x12\x00\x00", b"\x05\x12\x00\x00"):
+        with pytest.raises(pkg.SnappyB200Error):
+            ctx.uncompress(s)
+    f1, f2 = b"012345689abcdefghijklmnopqrstuvwxyz", b"some other string"
+    n2 = 100000 // len(f2)
+    src = f1 + f2 * n2
+    length = 2 * len(f1) + n2 * len(f2)
+
+    def varint(v):
+        out = bytearray()
+        while v >= 128:
+            out.append((v & 0x7f) | 0x80); v >>= 7
+        out.append(v)
+        return bytes(out)
+
+    def literal(b):
+        return bytes([(len(b) - 1) << 2]) + b                       # both fragments are shorter than 60 bytes
+
+    comp = varint(length) + literal(f1) + literal(f2) * n2
+    comp += bytes([3 | ((len(f1) - 1) << 2)]) + len(src).to_bytes(4, "little")      # copy-4: offset = everything so far
+    assert ctx.uncompress(comp) == src + f1
+
+
+def test_rocc_uncompress_operands_are_checked(pkg):
+    """the UNCOMPRESS command of the RoCC object must refuse operands outside its memory and a
+    stream whose preamble announces more than fits behind rs2."""
+    dev = pkg.RoccDevice(1 << 20)
+    try:
+        comp = pkg.default_context().compress(corpus.THISTLE)
+        dev.load_mem(comp, 0)
+
+        def run(rs1, length, rs2):
+            dev.poke_cmd(dev.SET_LENGTH, length, 0)
+            dev.step(1)
+            dev.poke_cmd(dev.UNCOMPRESS, rs1, rs2)
+            dev.step(1)
+            return dev.peek_resp_data()
+        assert run(0, len(comp), 4096) == 0 and dev.read_mem(4096, 130) == corpus.THISTLE
+        assert run(0, len(comp), (1 << 20) + 5) != 0                 # destination outside the memory
+        assert run((1 << 20) - 3, len(comp), 4096) != 0              # source runs off the end
+        assert run(0, len(comp), (1 << 20) - 64) != 0                # 130 bytes do not fit behind rs2
+        assert run(0, 1 << 30, 4096) != 0                            # poked length larger than the memory
+        big = b"\xff\xff\xff\xff\x0f" + b"\x00" * 16                 # preamble announces 4 GiB - 1
+        dev.load_mem(big, 0)
+        assert run(0, len(big), 4096) != 0
+    finally:
+        dev.close()
