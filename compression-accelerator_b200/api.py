@@ -201,9 +201,10 @@ class Context:
     # ---- ordering against torch's streams ------------------------------------------------
     # The library works on its own non-blocking stream.  Every entry that takes torch tensors first makes
     # that stream wait for torch's current stream (so a src still being produced by a torch op, or a dst
-    # torch has just allocated, is ready), tells the caching allocator the tensors are in use there, and
-    # afterwards makes torch's current stream wait for the library's work (so `out_n.item()`, slicing or
-    # freeing a result is ordered behind it without an explicit sync()).
+    # torch has just allocated, is ready) and afterwards makes torch's current stream wait for the
+    # library's work: `out_n.item()`, slicing, or freeing a tensor (the caching allocator reuses a block in
+    # the order of the stream it was allocated on) is then ordered behind the library's kernels without an
+    # explicit sync().
     def _ext(self):
         import torch
         if getattr(self, "_ext_stream", None) is None:
@@ -216,9 +217,6 @@ class Context:
         ext = self._ext()
         if cur.cuda_stream != ext.cuda_stream:
             ext.wait_stream(cur)
-            for t in tensors:
-                if t is not None:
-                    t.record_stream(ext)
 
     def _exit(self):
         import torch

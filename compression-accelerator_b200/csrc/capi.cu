@@ -55,7 +55,7 @@ constexpr int kParseStreams = 32;
 constexpr int kPipeParseStreams = 8;
 inline int pipe_streams() {
     static const int n = [] { const char* e = getenv("SNAPPY_B200_PARSE_STREAMS"); int v = e ? atoi(e) : kPipeParseStreams;
-                              return v < 1 ? 1 : v > kParseStreams ? kParseStreams : v; }();
+                              return v < 1 ? 1 : v > kParseStreams / 2 ? kParseStreams / 2 : v; }();
     return n;
 }
 
@@ -292,9 +292,21 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
                                            uint8_t* dst, size_t dst_cap, size_t* out_n, int mode) {
     const size_t cap = snappy_b200_max_compressed_length(n);
     const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
-    const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
-    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane);
+    // Which exact parser takes which chunk.  A lane-parser launch needs ~17 ms whatever its size (every
+    // fragment is one serial chain of DRAM round trips), the pipelined parser ~1.6 ms per 888 fragments.
+    // Behind a PCIe copy of ~20 ms per GiB that suggests: send the TAIL of the input first and give it to
+    // the lane parser (its latency hides under the rest of the transfer), then the head in order to the
+    // pipelined parser; elements are still emitted in stream order (head chunks as they finish, the tail
+    // last), so the bytes and the D2H drain do not change.  mode 5 forces the lane parser everywhere.
+    const bool lane_all = mode == kModeLane;
+    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane_all);
     const size_t n_chunks = (n + chunk - 1) / chunk;
+    static const int tail_pct = [] { const char* e = getenv("SNAPPY_B200_E2E_LANE_PCT"); return e ? atoi(e) : 33; }();
+    size_t k_split = n_chunks;                               // chunks [k_split, n_chunks) go to the lane parser
+    if (lane_all) k_split = 0;
+    else if (mode == SNAPPY_B200_EXACT && n_frag >= 4096 && tail_pct > 0)
+        k_split = n_chunks - (n_chunks * (size_t)(tail_pct > 100 ? 100 : tail_pct)) / 100;
+    const bool any_lane = k_split < n_chunks;
     const uint32_t hdr = sb::varint32_len((uint32_t)n);
     if (ensure_pipe(c, n_chunks) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(c->d_in.reserve(n + 64));
@@ -305,9 +317,9 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     CU(c->offsets.reserve((size_t)(n_frag + 1) * sizeof(unsigned long long)));
     uint8_t* d_in = (uint8_t*)c->d_in.p;
     uint8_t* d_out = (uint8_t*)c->d_out.p;
+    const uint32_t f_split = (uint32_t)(k_split * chunk / sb::kBlock);   // first fragment of the lane part
     uint32_t lane_epoch = 0;
-    if (lane && lane_begin(c, n_frag, sb::kBlock, &lane_epoch) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    const int n_ps = lane ? kParseStreams : pipe_streams();
+    if (any_lane && lane_begin(c, n_frag - f_split, sb::kBlock, &lane_epoch) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     // nothing of this call may overtake earlier work on the context's stream (shared scratch)
     CU(cudaEventRecord(c->ev_start, c->stream));
     CU(cudaStreamWaitEvent(c->s_h2d, c->ev_start, 0));
@@ -319,11 +331,9 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     static const bool prio_on = [] { const char* e = getenv("SNAPPY_B200_STREAM_PRIO"); return !e || atoi(e) != 0; }();
     cudaStream_t es = (mode == SNAPPY_B200_FAST || !prio_on) ? c->stream : c->s_emit;
     if (es != c->stream) CU(cudaStreamWaitEvent(es, c->ev_start, 0));
-    for (size_t k = 0; k < n_chunks; ++k) {
+    auto job_params = [&](size_t k) {
         const size_t lo = k * chunk, len = (n - lo < chunk) ? n - lo : chunk;
         const uint32_t f0 = (uint32_t)(lo / sb::kBlock);
-        CU(cudaMemcpyAsync(d_in + lo, src + lo, len, cudaMemcpyHostToDevice, c->s_h2d));
-        CU(cudaEventRecord(c->ev_h[k], c->s_h2d));
         sb::JobParams p;
         p.in = d_in + lo;
         p.n_total = len;
@@ -339,21 +349,48 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         p.out_stride = 0;
         p.offsets = (const unsigned long long*)c->offsets.p + f0;
         p.err = c->h_err_dev;
-        cudaStream_t ps = c->s_parse[k % n_ps];
+        return p;
+    };
+    // copy + parse of chunk k (the lane parser when k >= k_split), parse streams round robin per parser
+    auto copy_and_parse = [&](size_t k) -> snappy_b200_status {
+        const size_t lo = k * chunk, len = (n - lo < chunk) ? n - lo : chunk;
+        const uint32_t f0 = (uint32_t)(lo / sb::kBlock);
+        const bool lane = k >= k_split;
+        CU(cudaMemcpyAsync(d_in + lo, src + lo, len, cudaMemcpyHostToDevice, c->s_h2d));
+        CU(cudaEventRecord(c->ev_h[k], c->s_h2d));
+        const sb::JobParams p = job_params(k);
+        const int n_pipe_s = pipe_streams();
+        cudaStream_t ps = lane ? c->s_parse[lane_all ? k % kParseStreams : n_pipe_s + (k - k_split) % (kParseStreams - n_pipe_s)]
+                               : c->s_parse[k % n_pipe_s];
         CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
         if (lane)
-            CU(sb::launch_parse_lane(p, (uint8_t*)c->lane_pool.p + sb::lane_pool_bytes(f0, sb::kBlock), lane_epoch, ps,
-                                     &c->launches));
+            CU(sb::launch_parse_lane(p, (uint8_t*)c->lane_pool.p + sb::lane_pool_bytes(f0 - f_split, sb::kBlock), lane_epoch,
+                                     ps, &c->launches, /*beside_pipe=*/!lane_all));
         else CU(sb::launch_parse(p, kernel_mode(mode), ps, &c->launches));
         CU(cudaEventRecord(c->ev_p[k], ps));
+        return SNAPPY_B200_OK;
+    };
+    // sizes -> offsets -> elements of chunk k, in stream order on the emit stream
+    auto scan_and_emit = [&](size_t k) -> snappy_b200_status {
+        const sb::JobParams p = job_params(k);
+        const uint32_t f0 = (uint32_t)(k * chunk / sb::kBlock);
         CU(cudaStreamWaitEvent(es, c->ev_p[k], 0));
-        if (!lane) CU(sb::launch_size(p, es, &c->launches));
+        if (k < k_split) CU(sb::launch_size(p, es, &c->launches));      // the lane parser adds up sizes itself
         CU(sb::launch_scan(p.sizes, p.n_jobs, (unsigned long long*)c->offsets.p + f0, k == 0 ? hdr : 0,
                            (uint32_t)n, d_out, c->d_total, es, &c->launches,
                            k == 0 ? nullptr : c->d_total, c->h_run_dev + k));
         CU(sb::launch_emit(p, es, &c->launches));
         CU(cudaEventRecord(c->ev_e[k], es));
+        return SNAPPY_B200_OK;
+    };
+    for (size_t k = k_split; k < n_chunks; ++k)              // the tail crosses PCIe first
+        if (copy_and_parse(k) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    for (size_t k = 0; k < k_split; ++k) {
+        if (copy_and_parse(k) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+        if (scan_and_emit(k) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     }
+    for (size_t k = k_split; k < n_chunks; ++k)
+        if (scan_and_emit(k) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (es != c->stream) {                                   // the context's stream stays the call's timeline
         CU(cudaEventRecord(c->ev_done, es));
         CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));

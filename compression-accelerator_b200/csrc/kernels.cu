@@ -426,15 +426,28 @@ size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len) {
 }
 
 cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
-                              unsigned long long* launches) {
+                              unsigned long long* launches, bool beside_pipe) {
     if (p.n_jobs == 0) return cudaSuccess;
+    {   // the kernel's preferred carve-out follows the launch's company (alone: all L1; beside the pipelined
+        // parser: its maximum shared-memory split).  The attribute is per function, so it is switched here.
+        static int current = -2;
+        const int want = beside_pipe ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault;
+        if (want != current) {
+            cudaError_t e = cudaSuccess;
+#define SB_LANE_ATTR(V) if (lane_var() == V) e = cudaFuncSetAttribute(parse_lane_kernel<V>, cudaFuncAttributePreferredSharedMemoryCarveout, want);
+            SB_LANE_VARIANTS(SB_LANE_ATTR)
+#undef SB_LANE_ATTR
+            if (e != cudaSuccess) return e;
+            current = want;
+        }
+    }
     static_assert(sizeof(lane::Entry) == kLaneEntryBytes, "entry size");
     static const int fpw_env = env_int("SNAPPY_B200_LANE_FPW", 0), wpc_env = env_int("SNAPPY_B200_LANE_WPC", 0);
     LaneTable t;
     t.base = reinterpret_cast<uint8_t*>(pool);
     t.stride = table_entries(p.job_len);
     t.epoch = epoch;
-    t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 4u;
+    t.fpw = fpw_env >= 1 && fpw_env <= 32 ? (uint32_t)fpw_env : 3u;   // measured on 1 GiB text: 3 -> 21.9 ms, 4 -> 22.4, 8 -> 26.1, 2 -> 31 (registers)
     const uint32_t wpc = wpc_env >= 1 && wpc_env <= kLaneMaxThreads / 32 ? (uint32_t)wpc_env : 2u;
     const uint32_t per_cta = t.fpw * wpc, grid = (p.n_jobs + per_cta - 1) / per_cta;
 #define SB_LANE_CASE(V) case V: parse_lane_kernel<V><<<grid, 32 * wpc, 0, st>>>(p, t); break;

@@ -53,8 +53,10 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned
 // Writes seqs, nseq AND sizes (no size pass).  pool must hold lane_pool_bytes(n_jobs, job_len) bytes.
 constexpr uint32_t kLaneEntryBytes = 16;
 size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len);
+// beside_pipe: the launch shares the GPU with the pipelined parser's CTAs, so it asks for their (maximum)
+// shared-memory carve-out -- an SM cannot change its split while CTAs are resident.
 cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
-                              unsigned long long* launches);
+                              unsigned long long* launches, bool beside_pipe = false);
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 

@@ -89,6 +89,19 @@ def test_lane_host_entry_chunk_pipeline(ctx, oracle):
     assert comp == oracle.compress(data)
 
 
+def test_host_entry_tail_first_hybrid(ctx, oracle):
+    """Host entry, exact mode, >= 4096 fragments: the tail of the input crosses PCIe first and goes to the
+    lane parser, the head follows in order on the pipelined parser; the stream is still the reference's."""
+    n = (300 << 20) + 4321
+    host = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n)
+    host[(290 << 20):(290 << 20) + (2 << 20)] = corpus.random_ascii(2 << 20, 5)     # literal-heavy stretch in the tail
+    data = host.tobytes()
+    comp = ctx.compress(data)
+    want = oracle.compress(data)
+    assert len(comp) == len(want)
+    assert hashlib.sha256(comp).hexdigest() == hashlib.sha256(want).hexdigest()
+
+
 def test_large_stream_every_exact_engine(ctx, oracle):
     """256 MiB of concatenated MTG text through the default exact mode, the lane parser and the pipelined
     parser: each WHOLE stream equals the reference's, byte for byte."""
