@@ -293,15 +293,18 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     const size_t cap = snappy_b200_max_compressed_length(n);
     const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
     // Which exact parser takes which chunk.  A lane-parser launch needs ~17 ms whatever its size (every
-    // fragment is one serial chain of DRAM round trips), the pipelined parser ~1.6 ms per 888 fragments.
-    // Behind a PCIe copy of ~20 ms per GiB that suggests: send the TAIL of the input first and give it to
-    // the lane parser (its latency hides under the rest of the transfer), then the head in order to the
-    // pipelined parser; elements are still emitted in stream order (head chunks as they finish, the tail
-    // last), so the bytes and the D2H drain do not change.  mode 5 forces the lane parser everywhere.
+    // fragment is one serial chain of DRAM round trips), the pipelined parser ~1.6 ms per 888 fragments, so
+    // behind a PCIe copy of ~20 ms per GiB the chunks go to the pipelined parser.  SNAPPY_B200_E2E_LANE_PCT
+    // > 0 sends that share of the input FIRST (its tail) and gives it to the lane parser, whose latency
+    // then hides under the rest of the transfer; elements are still emitted in stream order (head chunks
+    // as they finish, the tail last), so bytes and drain do not change.  Measured on 1 GiB text: 0 % 37.4
+    // ms, 20 % 38.1, 33 % 38.6, 45 % 39.4 -- the two parsers slow each other down (the lane parser loses
+    // its L1 to the pipelined parser's shared-memory carve-out), so the default is 0.  mode 5 forces the
+    // lane parser everywhere (tests).
     const bool lane_all = mode == kModeLane;
     const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane_all);
     const size_t n_chunks = (n + chunk - 1) / chunk;
-    static const int tail_pct = [] { const char* e = getenv("SNAPPY_B200_E2E_LANE_PCT"); return e ? atoi(e) : 33; }();
+    static const int tail_pct = [] { const char* e = getenv("SNAPPY_B200_E2E_LANE_PCT"); return e ? atoi(e) : 0; }();
     size_t k_split = n_chunks;                               // chunks [k_split, n_chunks) go to the lane parser
     if (lane_all) k_split = 0;
     else if (mode == SNAPPY_B200_EXACT && n_frag >= 4096 && tail_pct > 0)
@@ -455,10 +458,6 @@ snappy_b200_status snappy_b200_create(snappy_b200_ctx** out, int device) {
         return fail(SNAPPY_B200_NO_DEVICE, "no CUDA device (libsnappy_b200 has no CPU path)", e);
     if (device < 0 || device >= count) return fail(SNAPPY_B200_INVALID_INPUT, "bad device ordinal");
     CU(cudaSetDevice(device));
-    {   // experiment knob: L2 <- DRAM fetch granularity (32 / 64 / 128 bytes); unset = driver default
-        const char* e = getenv("SNAPPY_B200_L2_FETCH");
-        if (e && atoi(e) > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
-    }
     std::call_once(g_init_once, [] { g_init_err = sb::kernels_init(); });
     if (g_init_err != cudaSuccess) return fail(SNAPPY_B200_CUDA_ERROR, "kernels_init", g_init_err);
     snappy_b200_ctx* c = new (std::nothrow) snappy_b200_ctx;

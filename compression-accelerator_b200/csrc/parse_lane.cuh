@@ -177,7 +177,7 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
                 e = M::ld_tab(slot);
                 M::st_tab(slot, mine, e.tag);
             }
-            M::prefetch_in(src, p + 192u, len);
+            M::prefetch_in(src, p + M::kAhead, len);
             if (kPfL2 || kSpec) {                                // the next probe if this one misses
                 const uint32_t g1 = (next == p + 1) ? fsr(own.x, own.y, 8) : load4<M>(src, next);
                 void* slot1 = M::slot(table, (g1 * kLaneMul) >> shift);
@@ -242,7 +242,8 @@ namespace sb {
 template <int kVar>
 struct LaneDev {
     static constexpr uint32_t kStride = (kVar & 8) ? 32u : 16u;
-    static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return __ldg(p); }
+    static constexpr uint32_t kAhead = (kVar & 128) ? 512u : 192u;   // input prefetch distance (bytes)
+    static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return (kVar & 64) ? *p : __ldg(p); }
     static __device__ __forceinline__ uint32_t ld_byte(const uint8_t* p) { return __ldg(p); }
     static __device__ __forceinline__ void* slot(void* table, uint32_t h) {
         return reinterpret_cast<uint8_t*>(table) + (size_t)h * kStride;

@@ -16,6 +16,7 @@
 namespace {
 
 struct Host {
+    static constexpr uint32_t kAhead = 192;
     static uint32_t ld_in(const uint32_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
     static uint32_t ld_byte(const uint8_t* p) { return *p; }
     static void* slot(void* table, uint32_t h) { return (sb::lane::Entry*)table + h; }
