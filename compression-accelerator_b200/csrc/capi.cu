@@ -851,7 +851,7 @@ snappy_b200_status snappy_b200_frame_uncompress_device(snappy_b200_ctx* c, const
         CU(cudaMemcpyAsync(&res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         if (res.error != 2 || pass) break;
-        max_records = (size_t)res.n_chunks;              /* the index was too small: now it is exact */
+        max_records = (size_t)res.n_all;                 /* the index was too small: now it is exact */
     }
     if (res.error) return fail(SNAPPY_B200_INVALID_INPUT, "malformed framed stream");
     if (res.out_bytes > dst_cap) return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < uncompressed length");

@@ -210,76 +210,164 @@ struct FrameIndex {                      // one record per data chunk, filled by
 };
 
 // index_base holds max_records records as parallel arrays (kFrameRecordBytes each, kernels.h):
-// in_off, out_off (u64), in_len, ulen, crc, kind, then the decode's got_len, got_crc (u32)
-struct FrameScratch { FrameIndex ix; uint32_t* got_len; uint32_t* got_crc; };
+// in_off, out_off (u64), in_len, ulen, crc, kind, then the decode's got_len, got_crc (u32), then the walk's
+// per-chunk scratch (every chunk of the stream, data or not): position (u64), payload length,
+// uncompressed length, CRC, kind (u32).
+struct FrameScratch {
+    FrameIndex ix; uint32_t* got_len; uint32_t* got_crc;
+    unsigned long long* t_pos; uint32_t* t_plen; uint32_t* t_ulen; uint32_t* t_crc; uint32_t* t_kind;
+};
 __host__ __device__ inline FrameScratch frame_scratch(void* base, uint64_t m) {
     FrameScratch f;
     f.ix.in_off = (unsigned long long*)base;
     f.ix.out_off = f.ix.in_off + m;
-    f.ix.in_len = (uint32_t*)(f.ix.out_off + m);
+    f.t_pos = f.ix.out_off + m;
+    f.ix.in_len = (uint32_t*)(f.t_pos + m);
     f.ix.ulen = f.ix.in_len + m;
     f.ix.crc = f.ix.ulen + m;
     f.ix.kind = f.ix.crc + m;
     f.got_len = f.ix.kind + m;
     f.got_crc = f.got_len + m;
+    f.t_plen = f.got_crc + m;
+    f.t_ulen = f.t_plen + m;
+    f.t_crc = f.t_ulen + m;
+    f.t_kind = f.t_crc + m;
     return f;
 }
+constexpr uint32_t kFrameNotData = 0xffffffffu;
 
-// The chunk chain is a linked list through the stream: one thread follows it (16 K hops per GiB).
-__global__ void frame_walk_kernel(const uint8_t* __restrict__ src, uint64_t n, FrameIndex ix,
-                                  uint64_t max_records, FrameWalkResult* res) {
-    if (threadIdx.x || blockIdx.x) return;
-    uint64_t pos = 0, out = 0, cnt = 0;
+// The chunk chain is a linked list through the stream (16 K hops per GiB).  Only the hop itself is
+// sequential -- the 4 bytes at a chunk's start give the next chunk's position -- so the walk is split:
+//   frame_hop_kernel    one warp, all lanes in step: position of every chunk.  A hop is ~25 instructions and
+//                       one round trip (two aligned words, the same in every lane); between hops one TMA bulk
+//                       prefetch per 32 KiB keeps the next 512 KiB of the stream on its way into L2, so that
+//                       round trip is an L2 hit.  (A lone warp runs one dependent instruction every ~6 cycles: the full parse of
+//                       a header, ~180 instructions, cost more per hop than the memory did.)
+//   frame_parse_kernel  one thread per chunk: identifier / type / length checks, CRC, the varint preamble
+//                       of the chunk's own stream (framing_format.txt:20-21, :68-78, :80-106, :122-128)
+//   frame_index_kernel  one CTA: data chunks compacted in order, output offsets by an exclusive scan
+__global__ void __launch_bounds__(32) frame_hop_kernel(const uint8_t* __restrict__ src, uint64_t n,
+                                                       unsigned long long* t_pos, uint64_t max_records,
+                                                       FrameWalkResult* res) {
+    const uint32_t lane = threadIdx.x;
+    uint64_t pos = 0, cnt = 0, pf = 0;
     uint32_t err = 0;
-    bool first = true;
+    const uintptr_t end = (uintptr_t)(src + n);
     while (pos < n) {
+        while (pf < n && pf < pos + (512u << 10)) {                          // stream -> L2: one TMA bulk prefetch
+            const uintptr_t b = ((uintptr_t)src + pf) & ~(uintptr_t)15;      // of 32 KiB per round (UBLKPF)
+            const uintptr_t e = (end & ~(uintptr_t)15) < b + 32768u ? (end & ~(uintptr_t)15) : b + 32768u;
+            if (lane == 0 && e > b)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b), "r"((uint32_t)(e - b)) : "memory");
+            pf += 32768;
+        }
         if (pos + 4 > n) { err = 1; break; }
-        const uint32_t type = src[pos];
-        const uint32_t len = src[pos + 1] | ((uint32_t)src[pos + 2] << 8) | ((uint32_t)src[pos + 3] << 16);
+        const uintptr_t a0 = (uintptr_t)(src + pos);
+        const uint32_t* wp = (const uint32_t*)(a0 & ~(uintptr_t)3);
+        const uint32_t w0 = __ldcg(wp), w1 = ((uintptr_t)(wp + 1) < end) ? __ldcg(wp + 1) : 0u;
+        const uint32_t len = __funnelshift_r(w0, w1, (uint32_t)(a0 & 3u) << 3) >> 8;
         if (pos + 4 + len > n) { err = 1; break; }
-        if (first && type != 0xff) { err = 1; break; }                       // :20-21
-        first = false;
-        if (type == 0xff) {                                                  // :68-78
-            const uint8_t id[6] = {0x73, 0x4e, 0x61, 0x50, 0x70, 0x59};
-            bool ok = len == 6;
-            for (uint32_t i = 0; ok && i < 6; ++i) ok = src[pos + 4 + i] == id[i];
-            if (!ok) { err = 1; break; }
-        } else if (type == 0x00 || type == 0x01) {
-            if (len < 4) { err = 1; break; }
-            const uint64_t pay = pos + 8;
-            const uint32_t plen = len - 4;
-            const uint32_t crc = src[pos + 4] | ((uint32_t)src[pos + 5] << 8) | ((uint32_t)src[pos + 6] << 16) |
-                                 ((uint32_t)src[pos + 7] << 24);
-            uint32_t ulen = plen;
-            if (type == 0x00) {                                              // varint32 preamble of the chunk's stream
-                ulen = 0;
-                uint32_t shift = 0, i = 0;
-                bool bad_varint = false;             // local: err may already be 2 (index full, keep counting)
-                for (;; ++i) {
-                    if (i >= plen || shift > 28) { bad_varint = true; break; }
-                    const uint32_t b = src[pay + i];
-                    if (shift == 28 && (b & 0x7fu) > 15u) { bad_varint = true; break; }
-                    ulen |= (b & 0x7fu) << shift;
-                    if (b < 128) break;
-                    shift += 7;
-                }
-                if (bad_varint) { err = 1; break; }
-            }
-            if (ulen > kFrameChunk) { err = 1; break; }                      // :88-91, :104-106
-            if (cnt < max_records) {
-                ix.in_off[cnt] = pay; ix.out_off[cnt] = out; ix.in_len[cnt] = plen;
-                ix.ulen[cnt] = ulen; ix.crc[cnt] = crc; ix.kind[cnt] = type;
-            } else if (!err) err = 2;
-            ++cnt;
-            out += ulen;
-        } else if (type >= 0x02 && type <= 0x7f) {                           // :122-128 unskippable
-            err = 1; break;
-        }                                                                    // 0x80..0xfe: skip (:111-120, :131-138)
+        if (cnt < max_records) { if (lane == 0) t_pos[cnt] = pos; }
+        else if (!err) err = 2;                                              // keep counting: the host retries
+        ++cnt;
         pos += 4 + (uint64_t)len;
     }
-    if (first && n) err = 1;
     if (n == 0) err = 1;                                                     // no stream identifier
-    res->n_chunks = cnt; res->out_bytes = out; res->error = err; res->pad = 0;
+    if (lane == 0) { res->n_all = cnt; res->n_chunks = 0; res->out_bytes = 0; res->error = err; }
+}
+
+__global__ void __launch_bounds__(256) frame_parse_kernel(const uint8_t* __restrict__ src, uint64_t n, FrameScratch f,
+                                                          uint64_t max_records, FrameWalkResult* res) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t cnt = res->n_all < max_records ? res->n_all : max_records;
+    if (i >= cnt || res->error == 1) return;
+    const uint64_t pos = f.t_pos[i];
+    const uintptr_t end = (uintptr_t)(src + n);
+    const uintptr_t a0 = (uintptr_t)(src + pos);
+    const uint32_t* wp = (const uint32_t*)(a0 & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(a0 & 3u) << 3;
+    uint32_t w[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) w[k] = ((uintptr_t)(wp + k) < end) ? __ldg(wp + k) : 0u;
+    const uint32_t d0 = __funnelshift_r(w[0], w[1], sh), d1 = __funnelshift_r(w[1], w[2], sh),
+                   d2 = __funnelshift_r(w[2], w[3], sh), d3 = __funnelshift_r(w[3], w[4], sh);
+    const uint32_t type = d0 & 0xffu, len = d0 >> 8;
+    bool bad = (i == 0 && type != 0xff);                                     // :20-21
+    uint32_t kind = kFrameNotData, plen = 0, ulen = 0;
+    if (type == 0xff) {                                                      // :68-78  "sNaPpY"
+        bad = bad || len != 6 || d1 != 0x50614e73u || (d2 & 0xffffu) != 0x5970u;
+    } else if (type == 0x00 || type == 0x01) {
+        if (len < 4) bad = true;
+        else {
+            kind = type; plen = len - 4; ulen = plen;
+            if (type == 0x00) {                                              // varint32 preamble of the chunk's stream
+                const unsigned long long vb = ((unsigned long long)d3 << 32) | d2;   // payload bytes 0..7
+                ulen = 0;
+                uint32_t shift = 0;
+                for (uint32_t k = 0;; ++k) {
+                    if (k >= plen || shift > 28) { bad = true; break; }
+                    const uint32_t bt = (uint32_t)(vb >> (8 * k)) & 0xffu;
+                    if (shift == 28 && (bt & 0x7fu) > 15u) { bad = true; break; }
+                    ulen |= (bt & 0x7fu) << shift;
+                    if (bt < 128) break;
+                    shift += 7;
+                }
+            }
+            if (ulen > kFrameChunk) bad = true;                              // :88-91, :104-106
+        }
+    } else if (type >= 0x02 && type <= 0x7f) {                               // :122-128 unskippable
+        bad = true;
+    }                                                                        // 0x80..0xfe: skip (:111-120, :131-138)
+    f.t_kind[i] = kind; f.t_plen[i] = plen; f.t_ulen[i] = bad ? 0u : ulen; f.t_crc[i] = d1;
+    if (bad) atomicExch(&res->pad, 1u);                                      // malformed (raised to error by the index pass)
+}
+
+__global__ void __launch_bounds__(1024) frame_index_kernel(FrameScratch f, uint64_t max_records, FrameWalkResult* res) {
+    __shared__ unsigned long long warp_sum[32];
+    __shared__ unsigned long long carry_s;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint64_t cnt = res->n_all < max_records ? res->n_all : max_records;
+    if (tid == 0) carry_s = 0;                       // hi 24 bits: data chunks so far, lo 40 bits: output bytes so far
+    __syncthreads();
+    const bool malformed = res->error == 1 || res->pad != 0;
+    if (!malformed) {
+        for (uint64_t base = 0; base < cnt; base += 1024) {
+            const uint64_t i = base + tid;
+            const bool data = i < cnt && f.t_kind[i] != kFrameNotData;
+            const unsigned long long v = data ? ((1ull << 40) | f.t_ulen[i]) : 0ull;
+            unsigned long long x = v;
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long y = __shfl_up_sync(kFull, x, d);
+                if (lane >= (uint32_t)d) x += y;
+            }
+            if (lane == 31) warp_sum[wid] = x;
+            __syncthreads();
+            if (wid == 0) {
+                unsigned long long sv = warp_sum[lane], t = sv;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const unsigned long long y = __shfl_up_sync(kFull, t, d);
+                    if (lane >= (uint32_t)d) t += y;
+                }
+                warp_sum[lane] = t - sv;
+            }
+            __syncthreads();
+            const unsigned long long excl = carry_s + warp_sum[wid] + (x - v);
+            if (data) {
+                const uint64_t j = excl >> 40;
+                f.ix.in_off[j] = f.t_pos[i] + 8; f.ix.out_off[j] = excl & ((1ull << 40) - 1);
+                f.ix.in_len[j] = f.t_plen[i]; f.ix.ulen[j] = f.t_ulen[i]; f.ix.crc[j] = f.t_crc[i]; f.ix.kind[j] = f.t_kind[i];
+            }
+            __syncthreads();
+            if (tid == 1023) carry_s = excl + v;
+            __syncthreads();
+        }
+    }
+    if (tid == 0) {
+        res->n_chunks = carry_s >> 40;
+        res->out_bytes = carry_s & ((1ull << 40) - 1);
+        if (malformed) res->error = 1;
+        res->pad = 0;
+    }
 }
 
 // stored vs recomputed CRC and decode status of every chunk -> one flag

@@ -571,8 +571,13 @@ cudaError_t launch_frame_headers(uint8_t* dst, const unsigned long long* offsets
 
 cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, uint64_t max_records,
                               FrameWalkResult* d_result, cudaStream_t st, unsigned long long* launches) {
-    frame_walk_kernel<<<1, 32, 0, st>>>(src, n, frame_scratch(index_base, max_records).ix, max_records, d_result);
-    if (launches) ++*launches;
+    const FrameScratch f = frame_scratch(index_base, max_records);
+    cudaError_t e = cudaMemsetAsync(d_result, 0, sizeof(FrameWalkResult), st);
+    if (e != cudaSuccess) return e;
+    frame_hop_kernel<<<1, 32, 0, st>>>(src, n, f.t_pos, max_records, d_result);
+    frame_parse_kernel<<<(uint32_t)((max_records + 255) / 256), 256, 0, st>>>(src, n, f, max_records, d_result);
+    frame_index_kernel<<<1, 1024, 0, st>>>(f, max_records, d_result);
+    if (launches) *launches += 3;
     return cudaGetLastError();
 }
 

@@ -101,11 +101,12 @@ cudaError_t launch_frame_bump(uint32_t* sizes, uint32_t n, cudaStream_t st, unsi
 cudaError_t launch_frame_headers(uint8_t* dst, const unsigned long long* offsets, const uint32_t* sizes,
                                  const uint32_t* crcs, uint32_t n, cudaStream_t st, unsigned long long* launches);
 // reader: chunk index (kFrameRecordBytes per record at index_base), decode + CRC check of all chunks
-constexpr size_t kFrameRecordBytes = 40;
+constexpr size_t kFrameRecordBytes = 64;
 struct FrameWalkResult {
-    unsigned long long n_chunks, out_bytes;
-    uint32_t error;                      // 0 ok, 1 malformed, 2 index too small (n_chunks is still exact)
-    uint32_t pad;
+    unsigned long long n_chunks, out_bytes;   // data chunks, bytes they decode to
+    unsigned long long n_all;                 // every chunk of the stream (exact also when the index was too small)
+    uint32_t error;                           // 0 ok, 1 malformed, 2 index too small: retry with max_records = n_all
+    uint32_t pad;                             // scratch of the walk kernels (a chunk's parse raises it)
 };
 cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, uint64_t max_records,
                               FrameWalkResult* d_result, cudaStream_t st, unsigned long long* launches);

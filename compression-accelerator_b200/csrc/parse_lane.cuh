@@ -148,8 +148,9 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
         const W3 f0 = load12<M>(src, 0);                         // what an empty entry stands for
         uint32_t p = 1, skip = 32;                               // snappy.cc:560, :587
         bool chain = false;                                      // probe right after a copy (snappy.cc:649-656)
-        bool have_spec = false;
+        bool have_spec = false, have_own = false;
         uint32_t h_prev = 0;
+        W3 own = f0;
         Entry spec = {0, 0, 0, 0}, mine_prev = {0, 0, 0, 0};
         for (;;) {
             uint32_t next;
@@ -162,11 +163,17 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
                 next = p + 1;
                 skip = 32;
             }
-            const W3 own = load12<M>(src, p);
+            if (!have_own) own = load12<M>(src, p);
             const uint32_t h = (own.x * kLaneMul) >> shift;
             void* slot = M::slot(table, h);
             Entry mine;
             mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
+            // The bytes of the next scan position are requested BEFORE the table access (next <= ip_limit, so
+            // the 12 bytes exist; loads issued behind an atomic wait for it, loads in front of it overlap):
+            // a missed probe continues without a round trip for its input, which matters once the skip is
+            // large and every probe lands on a cold line (literal-heavy input).
+            W3 own_next = own;
+            if (!(kVar & 128)) own_next = load12<M>(src, next);
             Entry e;                                             // snappy.cc:602-606 / :652-655: look up, then insert
             if (kSpec && have_spec) {
                 e = (h == h_prev) ? mine_prev : spec;
@@ -177,9 +184,9 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
                 e = M::ld_tab(slot);
                 M::st_tab(slot, mine, e.tag);
             }
-            M::prefetch_in(src, p + M::kAhead, len);
+            if (!(kVar & 64)) M::prefetch_in(src, p + M::kAhead, len);
             if (kPfL2 || kSpec) {                                // the next probe if this one misses
-                const uint32_t g1 = (next == p + 1) ? fsr(own.x, own.y, 8) : load4<M>(src, next);
+                const uint32_t g1 = (kVar & 128) ? load4<M>(src, next) : own_next.x;
                 void* slot1 = M::slot(table, (g1 * kLaneMul) >> shift);
                 if (kSpec) spec = M::ld_tab(slot1);
                 else M::prefetch_tab(slot1);
@@ -189,6 +196,8 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
             if (own.x != e.g0) {                                 // snappy.cc:607-608 / :656
                 p = next;
                 chain = false;
+                own = own_next;
+                have_own = !(kVar & 128);
                 if (kSpec) { have_spec = true; h_prev = h; mine_prev = mine; }
                 continue;
             }
@@ -207,6 +216,7 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
             M::st_tab(M::slot(table, (prev.x * kLaneMul) >> shift), ins, 0u);
             chain = true;
             have_spec = false;
+            have_own = false;
         }
     }
     if (next_emit < len) push<M>(out, len - next_emit, 0, 0);    // snappy.cc:665-668
@@ -242,8 +252,8 @@ namespace sb {
 template <int kVar>
 struct LaneDev {
     static constexpr uint32_t kStride = (kVar & 8) ? 32u : 16u;
-    static constexpr uint32_t kAhead = (kVar & 128) ? 512u : 192u;   // input prefetch distance (bytes)
-    static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return (kVar & 64) ? *p : __ldg(p); }
+    static constexpr uint32_t kAhead = 192u;                         // input prefetch distance (bytes)
+    static __device__ __forceinline__ uint32_t ld_in(const uint32_t* p) { return __ldg(p); }
     static __device__ __forceinline__ uint32_t ld_byte(const uint8_t* p) { return __ldg(p); }
     static __device__ __forceinline__ void* slot(void* table, uint32_t h) {
         return reinterpret_cast<uint8_t*>(table) + (size_t)h * kStride;

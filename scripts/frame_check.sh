@@ -1,0 +1,3 @@
+#!/bin/bash
+timeout 900 python -m pytest tests/test_framing.py -x -q -m gpu 2>&1 | tail -3
+timeout 300 python scripts/frame_one.py 2>&1 | tail -3
