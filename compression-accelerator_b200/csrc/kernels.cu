@@ -358,7 +358,7 @@ cudaError_t read_stats(unsigned long long* out16, bool reset) {
 
 // kVar values of parse_lane.cuh that are compiled in (40 is the product default; the others are kept for
 // A/B runs through SNAPPY_B200_LANE_VAR)
-#define SB_LANE_VARIANTS(X) X(0) X(2) X(32) X(34) X(40) X(42) X(104) X(168) X(232)
+#define SB_LANE_VARIANTS(X) X(0) X(2) X(32) X(34) X(40) X(42)
 
 cudaError_t kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -168,12 +168,11 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
             void* slot = M::slot(table, h);
             Entry mine;
             mine.tag = p | etag; mine.g0 = own.x; mine.g1 = own.y; mine.g2 = own.z;
-            // The bytes of the next scan position are requested BEFORE the table access (next <= ip_limit, so
-            // the 12 bytes exist; loads issued behind an atomic wait for it, loads in front of it overlap):
-            // a missed probe continues without a round trip for its input, which matters once the skip is
-            // large and every probe lands on a cold line (literal-heavy input).
-            W3 own_next = own;
-            if (!(kVar & 128)) own_next = load12<M>(src, next);
+            // The bytes of the next scan position are requested together with the table access (next <=
+            // ip_limit, so the 12 bytes exist): a missed probe continues without a round trip for its input,
+            // which matters once the skip is large and every probe lands on a cold line (literal-heavy
+            // input: 0.42 -> 0.34 ms for 256 MiB of random bytes).
+            const W3 own_next = load12<M>(src, next);
             Entry e;                                             // snappy.cc:602-606 / :652-655: look up, then insert
             if (kSpec && have_spec) {
                 e = (h == h_prev) ? mine_prev : spec;
@@ -184,9 +183,9 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
                 e = M::ld_tab(slot);
                 M::st_tab(slot, mine, e.tag);
             }
-            if (!(kVar & 64)) M::prefetch_in(src, p + M::kAhead, len);
+            M::prefetch_in(src, p + M::kAhead, len);
             if (kPfL2 || kSpec) {                                // the next probe if this one misses
-                const uint32_t g1 = (kVar & 128) ? load4<M>(src, next) : own_next.x;
+                const uint32_t g1 = own_next.x;
                 void* slot1 = M::slot(table, (g1 * kLaneMul) >> shift);
                 if (kSpec) spec = M::ld_tab(slot1);
                 else M::prefetch_tab(slot1);
@@ -197,7 +196,7 @@ SB_HD void parse_fragment(const uint8_t* src, uint32_t len, void* table, uint32_
                 p = next;
                 chain = false;
                 own = own_next;
-                have_own = !(kVar & 128);
+                have_own = true;
                 if (kSpec) { have_spec = true; h_prev = h; mine_prev = mine; }
                 continue;
             }
