@@ -568,8 +568,13 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "out_stride < max_compressed_length(len)");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (count == 0) return SNAPPY_B200_OK;
-    CU(c->seqs.reserve(count * sb::seq_stride((uint32_t)len) * sizeof(sb::seq_t) + 256));
-    CU(c->nseq.reserve((count + 1) * sizeof(uint32_t)));
+    // exact mode, buffers up to 2 KiB: one thread per buffer, parse and emission fused (parse_tiny.cuh)
+    static const bool tiny_on = [] { const char* e = getenv("SNAPPY_B200_TINY"); return !e || atoi(e) != 0; }();
+    const bool tiny = mode == SNAPPY_B200_EXACT && tiny_on && sb::tiny_takes((uint32_t)len);
+    if (!tiny) {
+        CU(c->seqs.reserve(count * sb::seq_stride((uint32_t)len) * sizeof(sb::seq_t) + 256));
+        CU(c->nseq.reserve((count + 1) * sizeof(uint32_t)));
+    }
     sb::JobParams p;
     p.in = (const uint8_t*)d_src;
     p.n_total = (count - 1) * in_stride + len;
@@ -587,6 +592,13 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.err = c->h_err_dev;
     const bool lane = lane_chosen(mode, count, (uint32_t)len);
     CU(cudaEventRecord(c->evp0, c->stream));
+    if (tiny) {
+        CU(sb::launch_tiny(p, c->stream, &c->launches));
+        CU(cudaEventRecord(c->evp1, c->stream));
+        CU(cudaEventRecord(c->evp2, c->stream));
+        c->staged = true;
+        return SNAPPY_B200_OK;
+    }
     if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
     else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));

@@ -16,6 +16,7 @@ namespace sb { __device__ unsigned long long g_stats[16]; }
 #include "parse_pipe.cuh"
 #include "parse_fast.cuh"
 #include "parse_lane.cuh"
+#include "parse_tiny.cuh"
 #include "emit.cuh"
 #include "decode.cuh"
 #include "decode_par.cuh"
@@ -379,6 +380,8 @@ cudaError_t kernels_init() {
     e = cudaFuncSetAttribute(decode_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(kStageWarps * (3 * kStageOutMax + 128)));
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTinySmemBytes);
+    if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCrcSmemBytes);
     if (e != cudaSuccess) return e;
     // The exchange kernels run beside the parser's CTAs: ask for the parser's shared-memory carve-out
@@ -456,6 +459,18 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
         default: return cudaErrorInvalidValue;
     }
 #undef SB_LANE_CASE
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- small buffers: one thread per buffer, parse + emission fused (parse_tiny.cuh) -------------------
+bool tiny_takes(uint32_t job_len) { return job_len <= tiny::kMaxLen; }
+
+cudaError_t launch_tiny(const JobParams& p, cudaStream_t st, unsigned long long* launches) {
+    if (p.n_jobs == 0) return cudaSuccess;
+    const uint32_t T = tiny_threads(p.job_len);
+    const size_t smem = (size_t)T * tiny::entries_for(p.job_len) * 2u;
+    tiny_kernel<<<(p.n_jobs + T - 1) / T, T, smem, st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -58,6 +58,11 @@ size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len);
 cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
                               unsigned long long* launches, bool beside_pipe = false);
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
+
+// Small buffers of a batch (exact mode, job_len <= 2048): one thread per buffer parses AND emits it
+// (parse_tiny.cuh); needs p.in / p.out / p.sizes only (no sequence lists, no size or emit pass).
+bool tiny_takes(uint32_t job_len);
+cudaError_t launch_tiny(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 cudaError_t launch_emit(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 
 // Exclusive scan of sizes[0..n_frag) (+hdr_len, + *carry_in when given) into offsets (uint64),
