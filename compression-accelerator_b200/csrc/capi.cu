@@ -568,7 +568,7 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "out_stride < max_compressed_length(len)");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (count == 0) return SNAPPY_B200_OK;
-    // exact mode, buffers up to 2 KiB: one thread per buffer, parse and emission fused (parse_tiny.cuh)
+    // exact mode, buffers up to 512 bytes: one thread per buffer, parse and emission fused (parse_tiny.cuh)
     static const bool tiny_on = [] { const char* e = getenv("SNAPPY_B200_TINY"); return !e || atoi(e) != 0; }();
     const bool tiny = mode == SNAPPY_B200_EXACT && tiny_on && sb::tiny_takes((uint32_t)len);
     if (!tiny) {

@@ -59,7 +59,7 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
                               unsigned long long* launches, bool beside_pipe = false);
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 
-// Small buffers of a batch (exact mode, job_len <= 2048): one thread per buffer parses AND emits it
+// Small buffers of a batch (exact mode, job_len <= 512): one thread per buffer parses AND emits it
 // (parse_tiny.cuh); needs p.in / p.out / p.sizes only (no sequence lists, no size or emit pass).
 bool tiny_takes(uint32_t job_len);
 cudaError_t launch_tiny(const JobParams& p, cudaStream_t st, unsigned long long* launches);
