@@ -1,4 +1,5 @@
 #!/bin/bash
-for v in 40 104 168 232; do echo "== var $v"; SNAPPY_B200_LANE_VAR=$v timeout 200 python scripts/run_one.py --data random --mib 256 --reps 4 --mode exact_lane | tail -1; done
-B=scripts/probes/randlat2.bin
-$B 2 0 0 4096 3 266 524288; $B 2 0 0 4096 3 2000 524288; $B 2 0 0 4096 8 266
+timeout 900 python -m pytest tests/test_lane_gpu.py -x -q 2>&1 | tail -2
+timeout 200 python scripts/run_one.py --mib 1024 --reps 4 --mode exact_lane | tail -2
+timeout 200 python scripts/run_one.py --data random --mib 1024 --reps 3 --mode exact_lane | tail -1
+timeout 200 python scripts/run_one.py --mib 2048 --reps 3 --mode exact_lane | tail -1
