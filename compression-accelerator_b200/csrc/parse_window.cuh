@@ -102,23 +102,52 @@ __device__ __forceinline__ uint32_t src_match_len(const Src& src, uint32_t a, ui
     }
 }
 
-// Serial scan (snappy.cc:587-608) over an accessor; see parse_serial.cuh.
+// The scan of a long run of misses (snappy.cc:587-608, entered with skip >= 64), 32 probes per warp step.
+// The probe positions depend only on (ip, skip) -- step = skip >> 5, skip += step (:590-597) -- so lane k
+// works out the k-th position of the schedule itself and all 32 probes are looked up and compared in
+// parallel: two round trips per 32 probes instead of two per probe (a matchless 64 KiB fragment is 266
+// probes, a 4 KiB page 155).  Exactness: probe k must see the inserts of probes 0..k-1; the table holds
+// everything older, and among the 32 a lane's candidate is the highest LOWER lane with its hash
+// (match.any), else the table entry.  Probes happen only up to the first hit, or up to the first position
+// whose successor passes ip_limit (:598); exactly those lanes insert, the highest lane of a slot winning as
+// in serial order.  Returns like the serial scan: true with (ip, cand) of the hit, false when the scan ran
+// off the fragment.
 template <class Src>
 __device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table, int shift,
                                                 uint32_t ip_limit, uint32_t& ip, uint32_t& skip,
-                                                uint32_t& cand) {
-    uint32_t nxt = ip;
+                                                uint32_t& cand, int lane) {
+    const uint32_t lt = (1u << lane) - 1u;
     for (;;) {
-        ip = nxt;
-        const uint32_t step = skip >> 5;
-        skip += step;
-        nxt = ip + step;
-        if (nxt > ip_limit) return false;
-        const uint32_t w = src.ld32(ip);
-        const uint32_t h = hash32(w, shift);
-        cand = table[h];
-        table[h] = (uint16_t)ip;
-        if (src.ld32(cand) == w) return true;
+        uint32_t pos = ip, sk = skip;                        // my probe: the lane-th of the schedule
+#pragma unroll 8
+        for (int j = 0; j < 31; ++j) {
+            const uint32_t st = sk >> 5;
+            if (j < lane) { sk += st; pos += st; }
+        }
+        const uint32_t step = sk >> 5, nxt = pos + step;     // :590-597 for my probe
+        const bool valid = nxt <= ip_limit;                  // :598 (positions grow with the lane: a prefix is valid)
+        uint32_t w = 0, h = 0x10000u + (uint32_t)lane;       // invalid lanes: a hash nobody shares
+        if (valid) { w = src.ld32(pos); h = hash32(w, shift); }
+        const uint32_t peers = __match_any_sync(kFull, h);
+        const uint32_t lower = peers & lt;
+        uint32_t c = valid ? table[h & 0xffffu] : 0u;
+        const uint32_t peer_pos = __shfl_sync(kFull, pos, lower ? 31 - __clz(lower) : lane);
+        if (lower) c = peer_pos;                             // an insert of this very batch shadows the table
+        const bool hit = valid && src.ld32(c) == w;
+        const uint32_t hits = __ballot_sync(kFull, hit), inval = __ballot_sync(kFull, !valid);
+        const uint32_t fh = hits ? (uint32_t)__ffs(hits) - 1u : 32u, fi = inval ? (uint32_t)__ffs(inval) - 1u : 32u;
+        const uint32_t n_probed = fh < fi ? fh + 1u : fi;    // lanes 0 .. n_probed-1 really probe (and insert, :606)
+        const uint32_t probed = lanes_below(n_probed);
+        if (((probed >> lane) & 1u) && (peers & probed & ~((2u << lane) - 1u)) == 0u) table[h] = (uint16_t)pos;
+        __syncwarp();
+        if (fh < fi) {
+            ip = __shfl_sync(kFull, pos, fh);
+            cand = __shfl_sync(kFull, c, fh);
+            return true;
+        }
+        if (fi < 32) return false;
+        ip = __shfl_sync(kFull, nxt, 31);                    // 32 misses: on with the schedule
+        skip = __shfl_sync(kFull, sk + step, 31);
     }
 }
 
@@ -236,7 +265,7 @@ struct WindowParser {
                     window_commit(table, h, pos, I, any_peer, lane);
                     if (vend < 32) {                         // 32 misses in a row: skip reached 64
                         uint32_t ip = wbase + vend, skip = 64, cand;
-                        if (!src_serial_scan(s, table, shift, ip_limit, ip, skip, cand)) return;
+                        if (!src_serial_scan(s, table, shift, ip_limit, ip, skip, cand, lane)) return;
                         const uint32_t matched = 4 + src_match_len(s, cand + 4, ip + 4, len, lane);
                         out->push(ip - next_emit, matched, ip - cand, lane);
                         ip += matched;
