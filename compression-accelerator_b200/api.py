@@ -45,6 +45,10 @@ SYMBOLS = {
                                               C.c_size_t, C.c_void_p, C.c_int]),
     "snappy_b200_compress_fragments_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t,
                                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]),
+    # no-allocation entry (no counterpart in the reference; static device scratch, inputs up to 1 MiB)
+    "snappy_b200_noalloc_max_input": (C.c_size_t, []),
+    "snappy_b200_compress_device_noalloc": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                                      C.c_void_p, C.c_void_p]),
     "snappy_b200_compress_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                                     C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p,
                                                     C.c_int]),

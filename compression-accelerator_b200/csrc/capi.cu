@@ -901,3 +901,108 @@ snappy_b200_status snappy_b200_frame_uncompress(snappy_b200_ctx* c, const void* 
 }
 
 }  // extern "C"
+
+/* ---- no-allocation entry point -----------------------------------------------------------------
+ * No counterpart in the reference; added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * snappy_b200_compress_device_noalloc is the exact-mode stream compressor of snappy_b200_compress_device
+ * for inputs up to SNAPPY_B200_NOALLOC_MAX_INPUT bytes (1 MiB = 16 fragments), with every piece of scratch
+ * the kernels need -- the fragments' sequence lists, their counts, sizes and output offsets -- in ONE
+ * file-scope device array instead of the context's cudaMalloc'ed buffers.  It needs no context, creates no
+ * stream or event, and calls no cudaMalloc / cudaFree / allocating routine: the caller passes input,
+ * output, the length word and the stream.  Same kernels, same launch sequence (parse_pipe_kernel<true>,
+ * size_block_kernel, scan_sizes_kernel, emit_kernel), so the stream is byte-identical to the existing
+ * entry's.
+ *
+ * The array is shared by every call on a device and keeps the last call's contents; the words that are
+ * read before this call's kernels have written them do not exist (every count, size and offset is written
+ * by a kernel of the call before a later kernel reads it), but the small header is cleared on the stream
+ * anyway so that a launch failure cannot leave a stale count behind.  Two calls that overlap on the GPU
+ * (different streams, or graphs replayed concurrently) RACE on the array: serialise them.
+ * Every GPU that loads the library holds the array (about 2 MiB) until the process exits. */
+namespace {
+
+constexpr size_t kNoAllocMaxInput = 1u << 20;                                  // bytes per call
+constexpr size_t kNoAllocMaxFrags = kNoAllocMaxInput / sb::kBlock;             // 16
+constexpr size_t kNoAllocSeqBytes = kNoAllocMaxFrags * (size_t)(sb::kBlock / 4 + 8) * sizeof(sb::seq_t);   // 2,098,176
+constexpr size_t kNoAllocHdrBytes = 3 * 256;                                   // nseq | sizes | offsets, 256 bytes each
+constexpr size_t kNoAllocScratchBytes = kNoAllocSeqBytes + kNoAllocHdrBytes;
+static_assert(kNoAllocSeqBytes % 256 == 0, "header must stay 256-byte aligned");
+static_assert((kNoAllocMaxFrags + 1) * sizeof(unsigned long long) <= 256, "offsets fit their slot");
+
+// In host code this NAME is a host-side stand-in, not a device address: never hand it to a kernel.  The
+// address comes from cudaGetSymbolAddress, once per device, with that device current (noalloc_scratch()).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Device address of the scratch array on the CURRENT device (set-up on first use per device).
+snappy_b200_status noalloc_scratch(unsigned char** out) {
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(SNAPPY_B200_INVALID_INPUT, "noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        cudaError_t e = sb::kernels_init();                  // function attributes (no allocation); idempotent
+        if (e != cudaSuccess) return fail(SNAPPY_B200_CUDA_ERROR, "noalloc: kernels_init", e);
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(SNAPPY_B200_CUDA_ERROR, "noalloc: cudaGetSymbolAddress(g_noalloc_scratch)", e);
+        g_noalloc_ptr[dev] = (unsigned char*)p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return SNAPPY_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t snappy_b200_noalloc_max_input(void) { return kNoAllocMaxInput; }
+
+snappy_b200_status snappy_b200_compress_device_noalloc(const void* d_src, size_t n, void* d_dst, size_t dst_cap,
+                                                       unsigned long long* d_out_n, void* cuda_stream) {
+    if (!d_dst || !d_out_n || (!d_src && n)) return fail(SNAPPY_B200_INVALID_INPUT, "null argument");
+    if (n > kNoAllocMaxInput) {
+        snprintf(g_err, sizeof g_err, "noalloc: input of %zu bytes exceeds the static scratch's maximum of %zu bytes "
+                 "(SNAPPY_B200_NOALLOC_MAX_INPUT); use snappy_b200_compress_device", n, kNoAllocMaxInput);
+        return SNAPPY_B200_INVALID_INPUT;
+    }
+    if (dst_cap < snappy_b200_max_compressed_length(n))
+        return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max_compressed_length(n)");
+    unsigned char* scratch = nullptr;
+    snappy_b200_status st = noalloc_scratch(&scratch);
+    if (st != SNAPPY_B200_OK) return st;
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    uint32_t* nseq = (uint32_t*)(scratch + kNoAllocSeqBytes);
+    uint32_t* sizes = (uint32_t*)(scratch + kNoAllocSeqBytes + 256);
+    unsigned long long* offsets = (unsigned long long*)(scratch + kNoAllocSeqBytes + 512);
+    const uint32_t n_frag = (uint32_t)((n + sb::kBlock - 1) / sb::kBlock);
+    sb::JobParams p;
+    p.in = (const uint8_t*)d_src;
+    p.n_total = n;
+    p.in_stride = sb::kBlock;
+    p.job_len = sb::kBlock;
+    p.n_jobs = n_frag;
+    p.seqs = (sb::seq_t*)scratch;
+    p.nseq = nseq;
+    p.sizes = sizes;
+    p.with_header = 0;
+    p.sparse = 0;
+    p.out = (uint8_t*)d_dst;
+    p.out_stride = 0;
+    p.offsets = offsets;
+    p.err = nullptr;
+    CU(cudaMemsetAsync(scratch + kNoAllocSeqBytes, 0, kNoAllocHdrBytes, stream));   // the shared header starts at zero
+    CU(sb::launch_parse(p, SNAPPY_B200_EXACT, stream, nullptr));
+    CU(sb::launch_size(p, stream, nullptr));
+    CU(sb::launch_scan(sizes, n_frag, offsets, sb::varint32_len((uint32_t)n), (uint32_t)n, (uint8_t*)d_dst, d_out_n,
+                       stream, nullptr));
+    CU(sb::launch_emit(p, stream, nullptr));
+    return SNAPPY_B200_OK;
+}
+
+}  // extern "C"

@@ -64,6 +64,21 @@ snappy_b200_status snappy_b200_compress_device(snappy_b200_ctx* ctx, const void*
                                                void* d_dst, size_t dst_cap,
                                                unsigned long long* d_out_n, int mode);
 
+/* ---- no-allocation entry.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Exact mode, one stream of n <= SNAPPY_B200_NOALLOC_MAX_INPUT
+ * bytes (1 MiB), byte-identical to snappy_b200_compress_device; asynchronous on `cuda_stream` (a
+ * cudaStream_t, may be 0).  Needs no context and allocates nothing: its scratch (sequence lists,
+ * counts, sizes, offsets; about 2 MiB) is a static device array that every GPU loading the library
+ * holds until exit.  All calls on a device share that array: calls that overlap on the GPU race --
+ * serialise them (one stream, or events).  n beyond the maximum -> SNAPPY_B200_INVALID_INPUT with
+ * snappy_b200_last_error() naming the limit.  dst_cap >= snappy_b200_max_compressed_length(n). */
+#define SNAPPY_B200_NOALLOC_MAX_INPUT ((size_t)1 << 20)
+size_t snappy_b200_noalloc_max_input(void);
+snappy_b200_status snappy_b200_compress_device_noalloc(const void* d_src, size_t n, void* d_dst,
+                                                       size_t dst_cap, unsigned long long* d_out_n,
+                                                       void* cuda_stream);
+
 /* ---- fragment-range entry (multi-GPU building block): compress n bytes that are a run of
  * whole 64 KiB fragments of a larger stream (only the last rank's run may end short) WITHOUT
  * the varint header; the payload lands contiguous at d_dst, its size in *d_out_n.  Rank r's
