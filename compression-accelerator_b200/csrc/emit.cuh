@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(128) size_kernel(JobParams p) {            // 
     if (job >= p.n_jobs) return;
     const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
     const uint32_t n = p.nseq[job];
+    if (n == kSeqEmitted) return;                                            // sizes[job] is final already
     uint32_t sum = 0;
     for (uint32_t i = lane; i < n; i += 32) sum += seq_encoded_size(q[i]);
     for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
@@ -42,6 +43,7 @@ __global__ void __launch_bounds__(kSizeThreads) size_block_kernel(JobParams p) {
     const uint32_t tid = threadIdx.x, job = blockIdx.x;
     const seq_t* q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
     const uint32_t n = p.nseq[job];
+    if (n == kSeqEmitted) return;
     uint32_t sum = 0;
     for (uint32_t i = tid; i < n; i += kSizeThreads) sum += seq_encoded_size(q[i]);
     for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
@@ -93,11 +95,12 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(JobParams p) {
     __shared__ uint32_t long_src[kMaxLong], long_dst[kMaxLong], long_len[kMaxLong];
     __shared__ uint32_t n_long;
     const uint32_t job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t n = p.nseq[job];
+    if (n == kSeqEmitted) return;                            // the parse kernel wrote this job's stream (whole CTA leaves)
     const uint32_t len = job_len_of(p, job);
     const uint8_t* __restrict__ in = p.in + (uint64_t)job * p.in_stride;
     uint8_t* __restrict__ out = p.out + (p.offsets ? p.offsets[job] : (uint64_t)job * p.out_stride);
     const seq_t* __restrict__ q = p.seqs + (uint64_t)job * seq_stride(p.job_len);
-    const uint32_t n = p.nseq[job];
     uint32_t hdr = 0;
     if (p.with_header) {
         hdr = varint32_len(len);

@@ -60,6 +60,18 @@ __device__ __forceinline__ void stage_fragment(const uint8_t* __restrict__ src, 
     if (bulk) mbar_wait(bar, 0);
 }
 
+// The job is one literal: preamble (snappy.cc:1006-1009) + EmitLiteral (:337-378) from the staged copy.
+__device__ __noinline__ void emit_one_literal(uint8_t* dst, uint32_t with_header, uint32_t* size_slot, uint32_t* nseq_slot,
+                                              uint32_t len, const uint8_t* s_in, int lane) {
+    uint32_t op = 0;
+    if (with_header) {
+        op = varint32_len(len);
+        if (lane == 0) put_varint32(dst, len);
+    }
+    op = warp_emit_literal(dst, op, s_in, 0, len, lane);
+    if (lane == 0) { *size_slot = op; *nseq_slot = kSeqEmitted; }
+}
+
 // One warp (one CTA) per job.  Packing several page-sized jobs into one CTA to spread the per-CTA
 // shared-memory reservation (18 instead of 17 4 KiB pages per SM) was measured and lost: a CTA's
 // resources return only when its slowest job ends, and the kernel compiled for more than one warp per
@@ -77,8 +89,16 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     stage_fragment(p.in + (uint64_t)job * p.in_stride, len, s_in, table, entries, bar, lane);
     SeqWriter out{p.seqs + (uint64_t)job * seq_stride(p.job_len), 0};
     const int shift = 32 - (31 - __clz(entries));           // snappy.cc:548
-    if (kWindow) parse_fragment_window(SmemSrc{s_in}, len, table, shift, out, lane);
+    bool one_literal = false;
+    if (kWindow) one_literal = parse_fragment_window(SmemSrc{s_in}, len, table, shift, out, lane);
     else parse_fragment_serial(s_in, len, table, shift, out, lane);
+    // Batch path (every job at its fixed slot, no scan of sizes needed): a job that parsed to ONE literal --
+    // incompressible data -- is written here, from the copy staged in shared memory, so that the emit kernel
+    // does not read it from DRAM a second time (snappy.cc:1006-1009 preamble, :337-378 EmitLiteral).
+    if (kWindow && one_literal && !p.offsets && !p.sparse) {
+        emit_one_literal(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len, s_in, lane);
+        return;
+    }
     if (lane == 0) p.nseq[job] = out.n;
 }
 
@@ -322,6 +342,7 @@ __global__ void __launch_bounds__(128) check_seqs_kernel(JobParams p, unsigned l
     const uint32_t job = blockIdx.x * 128 + threadIdx.x;
     if (job >= p.n_jobs) return;
     const uint32_t len = job_len_of(p, job), n = p.nseq[job], cap = seq_stride(p.job_len);
+    if (n == kSeqEmitted) return;                             // written by the parse kernel itself
     const seq_t* q = p.seqs + (uint64_t)job * cap;
     unsigned long long sum = 0;
     bool bad = n > cap;

@@ -24,6 +24,11 @@ __host__ __device__ inline uint32_t seq_lit(seq_t s) { return (uint32_t)s & 0x1f
 __host__ __device__ inline uint32_t seq_len(seq_t s) { return (uint32_t)(s >> 17) & 0xffffu; }
 __host__ __device__ inline uint32_t seq_off(seq_t s) { return (uint32_t)(s >> 33) & 0xffffu; }
 
+// nseq[job] of a job whose stream the parse kernel has already written itself (batch path: a page that
+// parsed to ONE literal is emitted from the staged copy in shared memory, kernels.cu parse_kernel); the
+// size and emit kernels leave such a job alone (sizes[job] is final).
+constexpr uint32_t kSeqEmitted = 0xffffffffu;
+
 // Sequences a job of `job_len` input bytes can produce: every copy consumes >= 4 bytes.
 __host__ __device__ inline uint32_t seq_stride(uint32_t job_len) { return job_len / 4 + 8; }
 

@@ -321,7 +321,7 @@ struct PipeResolver {
                         ++st_serial;
 #endif
                         ip = wbase + vend;
-                        if (!src_serial_scan(src, table, shift, ip_limit, ip, skip, cand, lane)) return;
+                        if (!src_serial_scan_call(src, table, shift, ip_limit, ip, skip, cand, lane)) return;
                         const uint32_t matched = 4 + src_match_len(src, cand + 4, ip + 4, len, lane);
                         push(ip - next_emit, matched, ip - cand);
                         ip += matched;

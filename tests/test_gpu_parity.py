@@ -115,6 +115,26 @@ def test_batch_size_sweep(ctx, oracle, length):
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
 
 
+@pytest.mark.parametrize("length", [513, 600, 1000, 4096, 4097, 8192])
+def test_batch_incompressible_pages_emitted_by_the_parser(ctx, oracle, length):
+    """A page that parses to ONE literal is written by the parse kernel itself (from shared memory); its
+    neighbours go through the size / emit kernels.  Mixed batch, ragged stride, every stream vs the oracle."""
+    count = 48
+    stride = length + 5
+    rnd = corpus.random_ascii(stride * count, 77)
+    txt = np.frombuffer((corpus.fixture("alice29.txt") * 4)[:stride * count], dtype=np.uint8)
+    buf = rnd.copy()
+    for i in range(count):
+        if i % 3 == 1:                                        # every third buffer is text
+            buf[i * stride:(i + 1) * stride] = txt[i * stride:(i + 1) * stride]
+        elif i % 3 == 2:                                      # and every third is random bytes of all 256 values
+            buf[i * stride:(i + 1) * stride] = np.random.default_rng(i).integers(0, 256, stride, dtype=np.uint8)
+    out, ostride, sizes = ctx.compress_batch(buf, length, stride, count)
+    for i in range(count):
+        want = oracle.compress(bytes(buf[i * stride:i * stride + length]))
+        assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
+
+
 @pytest.mark.parametrize("count", [1, 2, 5, 7])
 def test_batch_few_pages(ctx, oracle, count):
     """Page jobs share a CTA (several warps, one job each): counts that leave warps of the last CTA idle."""
