@@ -857,9 +857,21 @@ snappy_b200_status snappy_b200_frame_uncompress_device(snappy_b200_ctx* c, const
     uint32_t* d_bad = (uint32_t*)((uint8_t*)c->frame_res.p + 64);
     sb::FrameWalkResult res;
     size_t max_records = 2 * (dst_cap >> 16) + 1024;
+    // Fused reader (frame.cuh): the chain walk and the chunk decode in one kernel.  It pays when there are more
+    // chunks than warp slots, so that decoding early chunks overlaps the rest of the walk; with fewer chunks
+    // the separate walk is quicker (the hop is ~2x slower beside running decoders) and every chunk decodes at
+    // once behind it.  Measured, ms fused / separate: 128 MiB 6.0 / 5.3, 256 MiB 8.6 / 7.1, 512 MiB 11.3 /
+    // 12.3, 1 GiB 17.9 / 22.8.  SNAPPY_B200_FRAME_FUSED = 0 / 1 forces one or the other.
+    static const int fused_env = [] { const char* e = getenv("SNAPPY_B200_FRAME_FUSED"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
+    const bool fused = fused_env >= 0 ? fused_env == 1 : (dst_cap >> 16) >= 6144;
+    void* d_ctl = (uint8_t*)c->frame_res.p + 128;
     for (int pass = 0;; ++pass) {
         CU(c->frame_ix.reserve(max_records * sb::kFrameRecordBytes + 64));
-        CU(sb::launch_frame_walk((const uint8_t*)d_src, n, c->frame_ix.p, max_records, d_res, c->stream, &c->launches));
+        if (fused)
+            CU(sb::launch_frame_fused((const uint8_t*)d_src, n, (uint8_t*)d_dst, dst_cap, c->frame_ix.p, max_records, d_res,
+                                      d_ctl, c->stream, &c->launches));
+        else
+            CU(sb::launch_frame_walk((const uint8_t*)d_src, n, c->frame_ix.p, max_records, d_res, c->stream, &c->launches));
         CU(cudaMemcpyAsync(&res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         if (res.error != 2 || pass) break;
@@ -870,7 +882,7 @@ snappy_b200_status snappy_b200_frame_uncompress_device(snappy_b200_ctx* c, const
     if (res.n_chunks > 0xffffffffull) return fail(SNAPPY_B200_INVALID_INPUT, "too many chunks");
     CU(cudaMemsetAsync(d_bad, 0, sizeof(uint32_t), c->stream));
     CU(sb::launch_frame_decode((const uint8_t*)d_src, (uint8_t*)d_dst, c->frame_ix.p, max_records,
-                               (uint32_t)res.n_chunks, d_bad, c->stream, &c->launches));
+                               (uint32_t)res.n_chunks, d_bad, c->stream, &c->launches, fused));
     uint32_t bad = 0;
     CU(cudaMemcpyAsync(&bad, d_bad, sizeof(bad), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));

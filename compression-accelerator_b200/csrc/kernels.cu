@@ -617,19 +617,37 @@ cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, 
     return cudaGetLastError();
 }
 
+cudaError_t launch_frame_fused(const uint8_t* src, uint64_t n, uint8_t* dst, uint64_t dst_cap, void* index_base,
+                               uint64_t max_records, FrameWalkResult* d_result, void* d_ctl, cudaStream_t st,
+                               unsigned long long* launches) {
+    const FrameScratch f = frame_scratch(index_base, max_records);
+    cudaError_t e = cudaMemsetAsync(d_result, 0, sizeof(FrameWalkResult), st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(d_ctl, 0, sizeof(FrameFusedCtl), st);
+    if (e != cudaSuccess) return e;
+    const uint64_t want = (max_records + 2 + 3) / 4 + 1;                // warps for every record + the two of CTA 0
+    const uint32_t grid = (uint32_t)(want < 148ull * SB_DECODE_MINB ? want : 148ull * SB_DECODE_MINB);
+    frame_fused_kernel<<<grid, 128, 0, st>>>(src, n, dst, dst_cap, f, max_records, d_result, (FrameFusedCtl*)d_ctl);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_frame_decode(const uint8_t* src, uint8_t* dst, void* index_base, uint64_t max_records,
                                 uint32_t n_chunks, uint32_t* d_bad, cudaStream_t st,
-                                unsigned long long* launches) {
+                                unsigned long long* launches, bool decoded_already) {
     if (n_chunks == 0) return cudaSuccess;
     const FrameScratch f = frame_scratch(index_base, max_records);
-    DecodeParams p;
-    p.in = src; p.in_stride = 0; p.in_sizes = f.ix.in_len; p.in_size = 0; p.n_jobs = n_chunks;
-    p.out = dst; p.out_stride = 0; p.out_cap = 0; p.out_lens = f.got_len; p.out_len64 = nullptr;
-    p.in_offs = f.ix.in_off; p.out_offs = f.ix.out_off; p.caps = f.ix.ulen; p.kinds = f.ix.kind;
-    decode_kernel<<<(n_chunks + 3) / 4, 128, 0, st>>>(p);
-    if (launches) ++*launches;
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    cudaError_t e = cudaSuccess;
+    if (!decoded_already) {
+        DecodeParams p;
+        p.in = src; p.in_stride = 0; p.in_sizes = f.ix.in_len; p.in_size = 0; p.n_jobs = n_chunks;
+        p.out = dst; p.out_stride = 0; p.out_cap = 0; p.out_lens = f.got_len; p.out_len64 = nullptr;
+        p.in_offs = f.ix.in_off; p.out_offs = f.ix.out_off; p.caps = f.ix.ulen; p.kinds = f.ix.kind;
+        decode_kernel<<<(n_chunks + 3) / 4, 128, 0, st>>>(p);
+        if (launches) ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
     e = launch_crc32c_chunks(dst, f.ix.out_off, f.ix.ulen, 0, 0, 0, n_chunks, f.got_crc, st, launches);
     if (e != cudaSuccess) return e;
     frame_verify_kernel<<<(n_chunks + 255) / 256, 256, 0, st>>>(f.ix, f.got_len, f.got_crc, n_chunks, d_bad);

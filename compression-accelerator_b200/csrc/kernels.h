@@ -122,7 +122,13 @@ cudaError_t launch_frame_walk(const uint8_t* src, uint64_t n, void* index_base, 
                               FrameWalkResult* d_result, cudaStream_t st, unsigned long long* launches);
 cudaError_t launch_frame_decode(const uint8_t* src, uint8_t* dst, void* index_base, uint64_t max_records,
                                 uint32_t n_chunks, uint32_t* d_bad, cudaStream_t st,
-                                unsigned long long* launches);
+                                unsigned long long* launches, bool decoded_already = false);
+// reader, fused: chain walk + chunk decode in one kernel (frame.cuh); d_ctl = 16 bytes of device scratch.
+// Afterwards d_result is as after launch_frame_walk, and launch_frame_decode(..., decoded_already = true)
+// runs the CRC pass and the verification.
+cudaError_t launch_frame_fused(const uint8_t* src, uint64_t n, uint8_t* dst, uint64_t dst_cap, void* index_base,
+                               uint64_t max_records, FrameWalkResult* d_result, void* d_ctl, cudaStream_t st,
+                               unsigned long long* launches);
 
 cudaError_t kernels_init();  // one-time function attributes (dynamic shared memory opt-in)
 

@@ -2,11 +2,15 @@
 writer and the parallel, CRC-checked reader.  The reference vendors only the specification, so the
 checker is a CPU restatement (tests/oracle_lib.py frame_compress / frame_uncompress, CRC-32C in
 oracle/snappy_port.c) pinned by the RFC 3720 B.4 vectors the specification points at (:43-44)."""
+import os
+
 import numpy as np
 import pytest
 
 import corpus
 import oracle_lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 # RFC 3720 B.4 "CRC Examples": 32 bytes of zeroes, of ones, incrementing, decrementing
 RFC_VECTORS = [
@@ -222,3 +226,45 @@ def test_bytearray_input(ctx, oracle):
     assert framed == oracle_lib.frame_compress(bytes(data), oracle.compress)
     assert ctx.frame_uncompress(bytearray(framed)) == bytes(data)
     assert ctx.compress(data) == oracle.compress(bytes(data))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_frame_reader_both_paths(pkg, fused):
+    """The framed reader has two device paths (separate walk kernels + decode; walk and decode fused in one
+    kernel, the default for large streams).  Both must decode every chunk type, survive an index that is too
+    small on the first pass, and refuse malformed streams -- run in a fresh process with the path forced."""
+    import subprocess
+    import sys
+    code = r"""
+import os, sys
+sys.path.insert(0, os.path.join(%r, "tests")); sys.path.insert(0, %r)
+import corpus, oracle_lib
+import __graft_entry__ as g
+pkg = g.load_package(); ctx = pkg.Context(0); p = oracle_lib.port()
+def chunk(t, body): return bytes([t]) + len(body).to_bytes(3, "little") + body
+text = corpus.fixture("alice29.txt")
+a, b = b"hello framing " * 100, corpus.fixture("html")[:5000]
+s = oracle_lib.STREAM_ID + chunk(0x01, p.crc32c_masked(a).to_bytes(4, "little") + a) + chunk(0xfe, bytes(37)) + chunk(0x80, b"skip me")
+s += oracle_lib.STREAM_ID + chunk(0x00, p.crc32c_masked(b).to_bytes(4, "little") + p.compress(b)) + chunk(0xfd, b"")
+assert ctx.frame_uncompress(s) == a + b
+many, parts = bytearray(oracle_lib.STREAM_ID), []
+for i in range(3000):
+    piece = text[i * 40:i * 40 + 40]
+    many += chunk(0x00, p.crc32c_masked(piece).to_bytes(4, "little") + p.compress(piece)); parts.append(piece)
+assert ctx.frame_uncompress(bytes(many)) == b"".join(parts)
+big = (text * 40)[:5 << 20]
+good = ctx.frame_compress(big)
+assert ctx.frame_uncompress(good) == big
+for bad in (good[10:], good[:-5], good + bytes([0x02, 0, 0, 0]), good[:3000] + bytes([good[3000] ^ 1]) + good[3001:],
+            good[:70000] + bytes([0x03, 9, 0, 0]) + good[70004:]):
+    try:
+        ctx.frame_uncompress(bad)
+    except pkg.SnappyB200Error:
+        continue
+    raise AssertionError("a malformed framed stream was accepted")
+print("both-paths ok")
+""" % (ROOT, ROOT)
+    env = dict(os.environ, SNAPPY_B200_FRAME_FUSED=fused)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "both-paths ok" in r.stdout, (r.stdout[-2000:], r.stderr[-3000:])
