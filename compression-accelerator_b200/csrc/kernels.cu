@@ -237,6 +237,8 @@ __global__ void __launch_bounds__(32 * (2 + kFastMaxK), 2) parse_fast_kernel(Job
     const uint32_t bulk = (((uintptr_t)src & 15u) == 0) ? (len & ~15u) : 0u;
     if (tid == 0) {
         ctl->t_done = 0;
+        ctl->abort = 0;
+        ctl->err = p.err;
         if (bulk) {                                          // TMA bulk copy of the 16-byte aligned body
             mbar_init(&ctl->bar, 1);
             mbar_expect_tx(&ctl->bar, bulk);
@@ -288,6 +290,12 @@ __global__ void __launch_bounds__(32 * (2 + kFastMaxK), 2) parse_fast_kernel(Job
         }
         FSTAT_FLUSH(2, 2, lane); FSTAT_FLUSH(3, 3, lane); FSTAT_FLUSH(0, 4, lane); FSTAT_FLUSH(1, 5, lane);
     }
+    // A watchdog expired (FAST_WATCHDOG): whatever the roles left in the slot list is not to be trusted.
+    // With every slot empty the fragment is emitted as one literal -- a valid stream; the call itself fails
+    // through the context's error word.
+    __syncthreads();
+    if (ctl->abort)
+        for (uint32_t i = tid; i < sparse_slots(len); i += NT) slots[i] = 0u;
 }
 
 // ---- scan of fragment sizes + header ---------------------------------------------------------

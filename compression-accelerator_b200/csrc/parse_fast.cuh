@@ -72,7 +72,14 @@ __host__ __device__ inline uint32_t fast_evaluators(uint32_t job_len) {
 struct FastCtl {                           // first 128 bytes of shared memory
     uint64_t bar;                          // mbarrier of the TMA load
     volatile uint32_t t_done;              // windows whose candidates are in the ring
+    volatile uint32_t abort;               // a watchdog expired: every wait loop leaves, the fragment becomes one literal
+    unsigned int* err;                     // the context's error word (mapped host memory) or null
 };
+// The control block sits at the start of the kernel's dynamic shared memory: reachable from any role.
+__device__ __forceinline__ FastCtl* fast_ctl() {
+    extern __shared__ __align__(128) uint8_t fast_smem_base[];
+    return reinterpret_cast<FastCtl*>(fast_smem_base);
+}
 
 // sparse sequence slot: offset << 16 | (len - 4) << 2 | (position & 3); 0 = no copy starts here
 __host__ __device__ inline uint32_t sparse_pack(uint32_t pos, uint32_t len, uint32_t off) {
@@ -106,8 +113,16 @@ __device__ __forceinline__ void fast_backoff() {
     __nanosleep(SB_FAST_SLEEP);          // waiting warps must not eat the issue slots of the sequential roles
 #endif
 }
+// Inside a wait loop: leaves the loop (break) when a watchdog has expired anywhere in the CTA, or expires
+// itself -- raising the context's error word (the call then fails with SNAPPY_B200_CUDA_ERROR) instead of
+// trapping, which would poison the whole CUDA context.  The roles then run to their end on whatever they
+// hold, and the kernel turns the fragment into one literal (parse_fast_kernel's last lines).
 #define FAST_WATCHDOG(spins, what, a, b)                                                          \
-    do { if ((spins) > (1u << 24)) { if (lane == 0) printf("fast: %s blk %d %u %u\n", what, blockIdx.x, (unsigned)(a), (unsigned)(b)); __trap(); } } while (0)
+    if ((spins) > (1u << 24) || fast_ctl()->abort) {                                              \
+        FastCtl* wc_ = fast_ctl();                                                                \
+        if (!wc_->abort) { wc_->abort = 1u; if (wc_->err) *(volatile unsigned int*)wc_->err = 1u; } \
+        break;                                                                                    \
+    }
 
 // common prefix of s[a..] and s[b..] (b < end), at most `cap`, 128 bytes per round
 __device__ __forceinline__ uint32_t coop_match_capped(const uint8_t* s, uint32_t a, uint32_t b,
