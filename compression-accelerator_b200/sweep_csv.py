@@ -48,7 +48,7 @@ def scan(text: str):
         row = [c for c in rowf if c]
         if len(row) < 2 or row[0] == "type":
             continue
-        typ, length, cycles, clen = row[0], int(row[1]), int(row[2]), int(row[3])
+        typ, length, cycles, clen = row[0], int(row[1]), float(row[2]), int(row[3])   # csv_scan.py:16-20 uses float()
         res.setdefault(typ, {})[length] = (length / clen, cycles / length)
     return res
 

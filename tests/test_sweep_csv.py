@@ -53,3 +53,22 @@ def test_csv_from_device(pkg, oracle):
         assert cycles > 0
     res = sweep_csv.scan(sweep_csv.to_csv(rows))
     assert len(res["real"]) == 12
+
+
+def test_committed_bench_sweep_csv():
+    """profiles/r02_size_sweep.csv (written from bench.py's size sweep: every point's buffer replicated to
+    >= 1 GiB through the batch entry) parses the way benchmark/csv_scan.py:9-27 parses the reference's files,
+    covers the reference's 36 points, and carries the reference Snappy's compressed lengths."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "profiles", "r02_size_sweep.csv")).read()
+    assert text.splitlines()[0] == "type;length;cycles;compressed-length"
+    res = sweep_csv.scan(text)
+    assert sorted(res) == ["random", "real", "repeat"]                      # csv_scan.py:22-27 spellings
+    man = json.load(open(os.path.join(root, "tests", "golden", "manifest.json")))["sweep"]
+    for typ, rows in res.items():
+        assert sorted(rows) == sorted(corpus.SWEEP_SIZES)
+        for n, (ratio, cyc_per_byte) in rows.items():
+            want = man["%s-%d" % ("repeating" if typ == "repeat" else typ, n)]["compressed_n"]
+            assert abs(ratio - n / want) < 1e-12 and cyc_per_byte > 0
