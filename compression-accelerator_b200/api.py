@@ -19,7 +19,7 @@ LIB_PATH = os.environ.get("SNAPPY_B200_LIB") or os.path.join(_HERE, "libsnappy_b
 
 EXACT, FAST = 0, 1
 _MODES = {"exact": EXACT, "fast": FAST, "exact_serial": 2, "exact_window": 3, "exact_pipe_smem": 4, "exact_lane": 5,
-          "exact_pipe": 6, EXACT: EXACT, FAST: FAST, 2: 2, 3: 3, 4: 4, 5: 5, 6: 6}
+          "exact_pipe": 6, "exact_gtab": 7, EXACT: EXACT, FAST: FAST, 2: 2, 3: 3, 4: 4, 5: 5, 6: 6, 7: 7}
 OK, INVALID_INPUT, BUFFER_TOO_SMALL, CUDA_ERROR, NO_DEVICE = range(5)
 BLOCK = 65536            # tests/snappy/snappy.h:196 kBlockSize
 

@@ -67,6 +67,7 @@ struct snappy_b200_ctx {
     DevBuf seqs, nseq, sizes, offsets, d_in, d_out;
     DevBuf crcs, frame_ix, frame_res;          // framing: per-chunk CRCs, chunk index, walk result + flag
     DevBuf raw_ix;                             // segment / block index of one large raw stream (decode_par.cuh)
+    DevBuf gtab_pool;                          // uint16 tables of the global-table window parser (parse_gtab_kernel)
     DevBuf lane_pool;                          // fat hash tables of the lane parser (parse_lane.cuh), never cleared per call
     uint32_t lane_epoch = 0;                   // epoch of the pool's most recent launch (0 = pool all-empty)
     unsigned long long* d_total = nullptr;     // device
@@ -132,10 +133,10 @@ snappy_b200_status default_ctx(snappy_b200_ctx** out) {
 // parse, pipelined vs lane): 512 MiB 15.5 vs 18.5, 1 GiB 31.3 vs 22.4, 2 GiB 62 vs 40.7.  Running both
 // side by side on disjoint fragment ranges was measured and lost (22.1 ms per GiB: the pipelined CTAs
 // need the maximum shared-memory carve-out, which leaves the lane parser 28 KB of L1).
-constexpr int kModeLane = 5, kModePipe = 6;
+constexpr int kModeLane = 5, kModePipe = 6, kModeGtab = 7;
 constexpr size_t kLanePoolMaxBytes = 20ull << 30;
 inline uint32_t lane_min_frags() {
-    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 10240u; }();
+    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 13312u; }();
     return v;
 }
 inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
@@ -144,6 +145,33 @@ inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
            sb::lane_pool_bytes(n_jobs, job_len) <= kLanePoolMaxBytes;
 }
 inline int kernel_mode(int mode) { return mode == kModePipe ? (int)SNAPPY_B200_EXACT : mode; }
+
+// The third exact engine: the window parser with its uint16 tables in global memory (parse_gtab_kernel; one
+// warp per fragment, 28 per SM, input read in place).  6 ms per fragment and ~42 GB/s: between the pipelined
+// parser (1.6 ms, 34 GB/s, six fragments per SM) and the lane parser (17 ms floor, 46 GB/s).  Measured on
+// text, ms per parse (pipelined / global-table / lane): 64 MiB 2.9 / 3.2 / -, 128 MiB 4.6 / 4.2 / -, 256 MiB
+// 7.9 / 6.1 / -, 512 MiB 15.5 / 12.1 / 18.5, 768 MiB - / 18.1 / 19.8, 896 MiB - / 22.3 / 21.0, 1 GiB 31.4 /
+// 24.2 / 22.2.  Mode 7 forces it.
+inline uint32_t gtab_min_frags() {
+    static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_GTAB_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 1792u; }();
+    return v;
+}
+inline bool gtab_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
+    if (mode == kModeGtab) return true;
+    return mode == SNAPPY_B200_EXACT && job_len > 8192 && n_jobs >= gtab_min_frags() && !lane_chosen(mode, n_jobs, job_len);
+}
+// Tables + tickets of the global-table parser: `regions` disjoint sets of `tables` tables (one per concurrent
+// launch), tickets (one 256-byte slot per region) behind them.
+snappy_b200_status gtab_reserve(snappy_b200_ctx* c, uint32_t regions, uint32_t tables) {
+    CU(c->gtab_pool.reserve((size_t)regions * tables * sb::gtab_table_bytes() + (size_t)regions * 256));
+    return SNAPPY_B200_OK;
+}
+inline void* gtab_region(snappy_b200_ctx* c, uint32_t r, uint32_t tables) {
+    return (uint8_t*)c->gtab_pool.p + (size_t)r * tables * sb::gtab_table_bytes();
+}
+inline unsigned int* gtab_ticket(snappy_b200_ctx* c, uint32_t regions, uint32_t tables, uint32_t r) {
+    return (unsigned int*)((uint8_t*)c->gtab_pool.p + (size_t)regions * tables * sb::gtab_table_bytes() + (size_t)r * 256);
+}
 // Reserve the pool for `n_jobs` tables and open a new epoch (stream-ordered on c->stream).
 snappy_b200_status lane_begin(snappy_b200_ctx* c, uint64_t n_jobs, uint32_t job_len, uint32_t* epoch) {
     const size_t need = sb::lane_pool_bytes(n_jobs, job_len);
@@ -185,7 +213,7 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     if (n >= (1ull << 32)) return fail(SNAPPY_B200_INVALID_INPUT, "input of 2^32 bytes or more");
     if (mode != SNAPPY_B200_EXACT && mode != SNAPPY_B200_FAST && mode != 2 /* exact, serial parser */ &&
         mode != 3 /* exact, single-warp window parser */ && mode != 4 /* exact, pipelined, input in smem */ &&
-        mode != kModeLane && mode != kModePipe)
+        mode != kModeLane && mode != kModePipe && mode != kModeGtab)
         return fail(SNAPPY_B200_INVALID_INPUT, "unknown mode");
     if (dst_cap < (framed ? snappy_b200_frame_max_length(n) : snappy_b200_max_compressed_length(n)))
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "dst_cap < max length of the output");
@@ -215,8 +243,12 @@ snappy_b200_status compress_dev(snappy_b200_ctx* c, const void* d_src, size_t n,
     p.offsets = (const unsigned long long*)c->offsets.p;
     p.err = c->h_err_dev;
     const bool lane = lane_chosen(mode, n_frag, sb::kBlock);
+    const bool gtab = gtab_chosen(mode, n_frag, sb::kBlock);
+    if (gtab && gtab_reserve(c, 1, sb::gtab_tables()) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(cudaEventRecord(c->evp0, c->stream));
     if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
+    else if (gtab) CU(sb::launch_parse_gtab(p, gtab_region(c, 0, sb::gtab_tables()), sb::gtab_tables(),
+                                            gtab_ticket(c, 1, sb::gtab_tables(), 0), c->stream, &c->launches));
     else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
@@ -302,7 +334,10 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     // its L1 to the pipelined parser's shared-memory carve-out), so the default is 0.  mode 5 forces the
     // lane parser everywhere (tests).
     const bool lane_all = mode == kModeLane;
-    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane_all);
+    // Exact mode, 112 MiB and more: the chunks go to the global-table window parser (42 GB/s and 6 ms per
+    // fragment, against 34 GB/s for the pipelined parser): 32 MiB chunks, one table region per parse stream.
+    const bool use_gtab = mode == kModeGtab || (mode == SNAPPY_B200_EXACT && n_frag >= gtab_min_frags());
+    const size_t chunk = pipe_chunk_bytes(n, mode == SNAPPY_B200_FAST, lane_all || use_gtab);
     const size_t n_chunks = (n + chunk - 1) / chunk;
     static const int tail_pct = [] { const char* e = getenv("SNAPPY_B200_E2E_LANE_PCT"); return e ? atoi(e) : 0; }();
     size_t k_split = n_chunks;                               // chunks [k_split, n_chunks) go to the lane parser
@@ -323,6 +358,12 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
     const uint32_t f_split = (uint32_t)(k_split * chunk / sb::kBlock);   // first fragment of the lane part
     uint32_t lane_epoch = 0;
     if (any_lane && lane_begin(c, n_frag - f_split, sb::kBlock, &lane_epoch) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    // parse streams: 8 for the pipelined parser; 12 for the global-table parser, whose chunks have long tails
+    // (a fragment takes ~6 ms): measured 8 -> 31.4 ms per GiB end to end, 12 -> 30.6, 16 -> 30.7
+    static const bool streams_env = getenv("SNAPPY_B200_PARSE_STREAMS") != nullptr;
+    const int n_pipe_s = use_gtab && !streams_env ? 12 : pipe_streams();
+    const uint32_t g_regions = (uint32_t)n_pipe_s, g_tables = (uint32_t)(chunk / sb::kBlock);
+    if (use_gtab && gtab_reserve(c, g_regions, g_tables) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     // nothing of this call may overtake earlier work on the context's stream (shared scratch)
     CU(cudaEventRecord(c->ev_start, c->stream));
     CU(cudaStreamWaitEvent(c->s_h2d, c->ev_start, 0));
@@ -362,13 +403,15 @@ snappy_b200_status compress_host_pipelined(snappy_b200_ctx* c, const uint8_t* sr
         CU(cudaMemcpyAsync(d_in + lo, src + lo, len, cudaMemcpyHostToDevice, c->s_h2d));
         CU(cudaEventRecord(c->ev_h[k], c->s_h2d));
         const sb::JobParams p = job_params(k);
-        const int n_pipe_s = pipe_streams();
         cudaStream_t ps = lane ? c->s_parse[lane_all ? k % kParseStreams : n_pipe_s + (k - k_split) % (kParseStreams - n_pipe_s)]
                                : c->s_parse[k % n_pipe_s];
         CU(cudaStreamWaitEvent(ps, c->ev_h[k], 0));
         if (lane)
             CU(sb::launch_parse_lane(p, (uint8_t*)c->lane_pool.p + sb::lane_pool_bytes(f0 - f_split, sb::kBlock), lane_epoch,
                                      ps, &c->launches, /*beside_pipe=*/!lane_all));
+        else if (use_gtab)
+            CU(sb::launch_parse_gtab(p, gtab_region(c, (uint32_t)(k % n_pipe_s), g_tables), g_tables,
+                                     gtab_ticket(c, g_regions, g_tables, (uint32_t)(k % n_pipe_s)), ps, &c->launches));
         else CU(sb::launch_parse(p, kernel_mode(mode), ps, &c->launches));
         CU(cudaEventRecord(c->ev_p[k], ps));
         return SNAPPY_B200_OK;
@@ -483,7 +526,7 @@ void snappy_b200_destroy(snappy_b200_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->seqs.release(); c->nseq.release(); c->sizes.release(); c->offsets.release();
-    c->d_in.release(); c->d_out.release(); c->lane_pool.release();
+    c->d_in.release(); c->d_out.release(); c->lane_pool.release(); c->gtab_pool.release();
     c->crcs.release(); c->frame_ix.release(); c->frame_res.release(); c->raw_ix.release();
     if (c->d_total) cudaFree(c->d_total);
     if (c->h_total) cudaFreeHost(c->h_total);
@@ -591,6 +634,8 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     p.offsets = nullptr;
     p.err = c->h_err_dev;
     const bool lane = lane_chosen(mode, count, (uint32_t)len);
+    const bool gtab = gtab_chosen(mode, count, (uint32_t)len);
+    if (gtab && gtab_reserve(c, 1, sb::gtab_tables()) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     CU(cudaEventRecord(c->evp0, c->stream));
     if (tiny) {
         CU(sb::launch_tiny(p, c->stream, &c->launches));
@@ -600,6 +645,8 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
         return SNAPPY_B200_OK;
     }
     if (lane) { if (lane_parse_all(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR; }
+    else if (gtab) CU(sb::launch_parse_gtab(p, gtab_region(c, 0, sb::gtab_tables()), sb::gtab_tables(),
+                                            gtab_ticket(c, 1, sb::gtab_tables(), 0), c->stream, &c->launches));
     else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;

@@ -102,6 +102,39 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     if (lane == 0) p.nseq[job] = out.n;
 }
 
+// ---- window parser with the table in GLOBAL memory (kept L2-resident) and the input read in place ----------
+// No shared memory at all, so residency is set by registers and warp slots (up to ~28 warps per SM) instead of
+// by the 32 KB table (6 fragments per SM in parse_pipe_kernel).  A persistent grid of one-warp CTAs; CTA b owns
+// table b of the pool for its whole life (148 x W tables of 32 KB: W = 16 is 76 MB of the 126 MB L2) and takes
+// fragments from a ticket counter.  Only this warp ever touches its table, so plain (L1-cached) accesses are
+// coherent; each window costs two L2 round trips (table entries, candidate bytes) on top of the parser's own
+// instruction latency.
+__global__ void __launch_bounds__(32) parse_gtab_kernel(JobParams p, uint16_t* pool, unsigned int* ticket) {
+    const int lane = threadIdx.x;
+    uint16_t* table = pool + (size_t)blockIdx.x * kMaxTable;
+    for (;;) {
+        uint32_t job = 0;
+        if (lane == 0) job = atomicAdd(ticket, 1u);
+        job = __shfl_sync(kFull, job, 0);
+        if (job >= p.n_jobs) return;
+        const uint32_t len = job_len_of(p, job);
+        const uint32_t entries = table_entries(len);             // from THIS fragment's length
+        {
+            uint4* t4 = reinterpret_cast<uint4*>(table);
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            for (uint32_t i = lane; i < entries / 8; i += 32) t4[i] = z;
+        }
+        __syncwarp();
+        SeqWriter out{p.seqs + (uint64_t)job * seq_stride(p.job_len), 0};
+        const int shift = 32 - (31 - __clz(entries));
+        GlobalSrc src;
+        src.g = p.in + (uint64_t)job * p.in_stride;
+        parse_fragment_window(src, len, table, shift, out, lane);
+        if (lane == 0) p.nseq[job] = out.n;
+        __syncwarp();
+    }
+}
+
 // ---- pipelined parser: one resolver warp + P producer warps per fragment ----------------------
 // kGlobal = false: fragment staged in shared memory by TMA (2 fragments per SM).
 // kGlobal = true : producers gather the input from global memory; shared memory holds only the
@@ -488,6 +521,26 @@ cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cu
         default: return cudaErrorInvalidValue;
     }
 #undef SB_LANE_CASE
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- window parser, table in global memory ---------------------------------------------------------------
+// Warps (= tables) per SM.  Measured on 1 GiB of text, ms per parse: 8 -> 42.1, 16 -> 28.6, 24 -> 25.0, 28 -> 23.8,
+// 32 -> 26.1 (throughput per SM stops growing at 28: L1, L2 and DRAM all near 55 % busy, every window issues
+// ~330 uncoalesced L1 requests).
+uint32_t gtab_tables() {
+    static const int w = [] { const char* e = getenv("SNAPPY_B200_GTAB_W"); int v = e ? atoi(e) : 28; return v < 1 ? 1 : v > 32 ? 32 : v; }();
+    return 148u * (uint32_t)w;
+}
+size_t gtab_table_bytes() { return (size_t)kMaxTable * sizeof(uint16_t); }
+
+cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_tables, unsigned int* ticket, cudaStream_t st,
+                              unsigned long long* launches) {
+    if (p.n_jobs == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) return e;
+    parse_gtab_kernel<<<p.n_jobs < n_tables ? p.n_jobs : n_tables, 32, 0, st>>>(p, reinterpret_cast<uint16_t*>(tables), ticket);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -62,6 +62,15 @@ size_t lane_pool_bytes(uint64_t n_jobs, uint32_t job_len);
 // shared-memory carve-out -- an SM cannot change its split while CTAs are resident.
 cudaError_t launch_parse_lane(const JobParams& p, void* pool, uint32_t epoch, cudaStream_t st,
                               unsigned long long* launches, bool beside_pipe = false);
+// Window parser with its uint16 tables in global memory (parse_gtab_kernel), input read in place: a persistent
+// grid of min(n_jobs, n_tables) one-warp CTAs, CTA b using table b of `tables` (gtab_table_bytes() each) and
+// taking jobs from *ticket (a device word, zeroed by the launcher).  Concurrent launches need disjoint tables
+// and tickets.  gtab_tables() = tables that fill one GPU.  Writes seqs and nseq (sizes: launch_size).
+uint32_t gtab_tables();
+size_t gtab_table_bytes();
+cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_tables, unsigned int* ticket, cudaStream_t st,
+                              unsigned long long* launches);
+
 cudaError_t launch_size(const JobParams& p, cudaStream_t st, unsigned long long* launches);
 
 // Small buffers of a batch (exact mode, job_len <= 512): one thread per buffer parses AND emits it

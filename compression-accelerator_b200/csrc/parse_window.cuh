@@ -41,7 +41,10 @@ __device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return __funnelshi
 
 // ---- input accessors ------------------------------------------------------------------------
 struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
+    static constexpr bool kInPlace = false;
     const uint8_t* s;
+    __device__ __forceinline__ void prefetch(uint32_t) const {}
+    __device__ __forceinline__ void touch(uint32_t) const {}
     __device__ __forceinline__ uint32_t ld32(uint32_t pos) const { return lds32u(s, pos); }
     __device__ __forceinline__ uint32_t ld32_upto(uint32_t pos, uint32_t) const { return lds32u(s, pos); }
     __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
@@ -49,7 +52,18 @@ struct SmemSrc {                         // fragment staged in shared memory (4-
 };
 
 struct GlobalSrc {                       // fragment read in place from global memory
+    static constexpr bool kInPlace = true;
     const uint8_t* g;                    // fragment start (any alignment)
+    __device__ __forceinline__ void prefetch(uint32_t pos) const {       // the 128-byte line holding g[pos] -> L1
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(g + pos));
+    }
+    // One 32-byte SECTOR -> L1 (a load whose result nobody waits for).  prefetch.global.L1 moves whole lines:
+    // for 32 random candidates per window that is four times the traffic (ncu: 47.7 GB of DRAM reads for
+    // 512 MiB of input with line prefetches).
+    __device__ __forceinline__ void touch(uint32_t pos) const {
+        uint32_t unused;
+        asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(unused) : "l"((uintptr_t)(g + pos) & ~(uintptr_t)3));
+    }
     __device__ __forceinline__ uint32_t ld32(uint32_t pos) const {
         const uintptr_t a = (uintptr_t)(g + pos);
         const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
@@ -191,6 +205,18 @@ struct WindowParser {
     // per-window lane registers
     uint32_t pos, h, T, ml, ek, nx, Sk;
 
+    // The window's pending inserts I.  Shared-memory table: store, then settle same-slot lanes by reading back
+    // (window_commit).  Global-memory table: a read-back is an L2 round trip, so the winner of a slot -- its
+    // highest inserted lane, as in serial order -- is decided in registers from the same-hash mask.
+    __device__ __forceinline__ void commit(uint32_t I, uint32_t ph, bool any_peer) {
+        if constexpr (Src::kInPlace) {
+            if (((I >> lane) & 1u) && (ph & I & ~((2u << lane) - 1u)) == 0u) table[h] = (uint16_t)pos;
+            __syncwarp();
+        } else {
+            window_commit(table, h, pos, I, any_peer, lane);
+        }
+    }
+
     // Store the sequences of the fast copies in `chosen` (lane order = stream order).
     __device__ __forceinline__ void flush_chosen(uint32_t chosen, uint32_t lt) {
         const uint32_t prevmask = chosen & lt;
@@ -207,6 +233,7 @@ struct WindowParser {
         const uint32_t lt = (1u << lane) - 1u;
         uint32_t win = 0, sl = 1, I = 0;                    // first probe is position 1 (:560)
         int scan0 = 1;                                      // lane of probe #0 of the current scan
+        uint32_t tq = 0;                                    // in-place tables: entries looked up ahead (see below)
         for (;;) {                                          // one iteration per window
             // ---- parallel set-up -----------------------------------------------------------
             const uint32_t wbase = win << 5;
@@ -216,8 +243,10 @@ struct WindowParser {
             h = hash32(d0, shift);
             T = table[h];
             uint32_t c0, c1, c2, c3;
-            s.ld16(T, c0, c1, c2, c3);
-            const bool peer = (__match_any_sync(kFull, h) & lt) != 0;   // a lower lane has my hash
+            s.ld16(T, c0, c1, c2, c3);       // (in place: 4 bytes for all + 12 only for hitting lanes was measured and
+                                             // lost, 24.2 -> 26.1 ms per GiB: the second load is a dependent round trip)
+            const uint32_t ph = __match_any_sync(kFull, h);             // lanes with my hash
+            const bool peer = (ph & lt) != 0;                           // a lower lane has my hash
             const bool hit = (c0 == d0);
             {
                 uint32_t x1 = c1 ^ d1, x2 = c2 ^ d2, x3 = c3 ^ d3, m = 12;
@@ -232,6 +261,20 @@ struct WindowParser {
             const uint32_t L = __ballot_sync(kFull, hit || peer) & VPRE;           // lanes whose probe may hit
             const uint32_t SLOWM = __ballot_sync(kFull, peer || ml == 12);
             const bool any_peer = __any_sync(kFull, peer);
+            // In-place input and a table in global memory (parse_gtab_kernel): every window would start with two
+            // dependent L2 round trips (table entries, then candidate bytes).  Windows mostly follow one another,
+            // so both are taken off the critical path by speculation, two deep: at window w the entries of window
+            // w + 2 are looked up (the lines land in this SM's L1, which stays coherent for a table only this
+            // warp writes), and the entries looked up one window ago -- they have long arrived -- say which
+            // sectors to touch for the candidates of window w + 1.  The real look-up and the candidate read at
+            // the start of a window are then L1 hits; an entry changed by an insert in between is seen by the
+            // re-read and costs only that lane a miss, and after a jump the speculation is simply wasted.
+            if constexpr (Src::kInPlace) {
+                s.touch(tq); s.touch(tq + 15u);              // candidates of the next window (tq: table values < len)
+                const uint32_t p2 = pos + 64u;
+                tq = p2 < ip_limit ? (uint32_t)table[hash32(s.ld32(p2), shift)] : 0u;
+                if (lane == 0 && wbase + 256u < len) s.prefetch(wbase + 256u);   // the input itself, two lines ahead
+            }
             ek = lane + 4 + ml;                              // lane of ip after taking my copy
             {
                 const uint32_t ipk = pos + 4 + ml;
@@ -272,7 +315,7 @@ struct WindowParser {
                     const uint32_t upto = vend < vpre_end ? vend : vpre_end;
                     I |= lanes_from(sl) & lanes_below(upto) & ~SK;
                     if (vpre_end <= vend && inval) return;   // next probe would pass ip_limit (:598)
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(I, ph, any_peer);
                     if (vend < 32) {                         // 32 misses in a row: skip reached 64
                         uint32_t ip = wbase + vend, skip = 64, cand;
                         if (!src_serial_scan(s, table, shift, ip_limit, ip, skip, cand, lane)) return;
@@ -291,7 +334,7 @@ struct WindowParser {
                     return;
                 } else if (f & 64u) {                        // last copy leaves the window
                     I |= lanes_from(sl) & ~SK;
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(I, ph, any_peer);
                     const uint32_t ip = next_emit;
                     if (e_last == 32) { win += 1; sl = 0; scan0 = 1; I = 0; }
                     else {
@@ -316,7 +359,7 @@ struct WindowParser {
                     const uint32_t e = ip - wbase;
                     if (e <= 32) I |= 1u << (e - 1);         // insert ip-1 (:649-651)
                     if (e < 32) { sl = e; scan0 = (int)e + 1; continue; }
-                    window_commit(table, h, pos, I, any_peer, lane);
+                    commit(I, ph, any_peer);
                     if (e == 32) { win += 1; sl = 0; scan0 = 1; I = 0; }
                     else {
                         const uint32_t a = (ip - 1) & 31u;
