@@ -158,7 +158,9 @@ inline uint32_t gtab_min_frags() {
 }
 inline bool gtab_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
     if (mode == kModeGtab) return true;
-    return mode == SNAPPY_B200_EXACT && job_len > 8192 && n_jobs >= gtab_min_frags() && !lane_chosen(mode, n_jobs, job_len);
+    // batch buffers: over 4 KiB (8 KiB text buffers 72 vs 49 GB/s for the shared-memory page parser, which fits
+    // only nine of them per SM; at 4 KiB the two tie and the page parser stays)
+    return mode == SNAPPY_B200_EXACT && job_len > 4096 && n_jobs >= gtab_min_frags() && !lane_chosen(mode, n_jobs, job_len);
 }
 // Tables + tickets of the global-table parser: `regions` disjoint sets of `tables` tables (one per concurrent
 // launch), tickets (one 256-byte slot per region) behind them.

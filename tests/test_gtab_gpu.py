@@ -77,10 +77,11 @@ def test_gtab_batch_sizes(ctx, oracle, length):
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
 
 
-def test_batch_of_large_buffers_takes_gtab_by_default(ctx, oracle):
-    """Exact mode, buffers over 8 KiB, 1,792 and more of them: the batch entry picks the global-table parser."""
+@pytest.mark.parametrize("length", [4097, 8192, 20000])
+def test_batch_of_large_buffers_takes_gtab_by_default(ctx, oracle, length):
+    """Exact mode, buffers over 4 KiB, 1,792 and more of them: the batch entry picks the global-table parser."""
     text = corpus.fixture("all-mtg-cards.txt")
-    length, count = 20000, 2000
+    count = 2000
     buf = np.frombuffer((text * 14)[:length * count], dtype=np.uint8).copy()
     out, ostride, sizes = ctx.compress_batch(buf, length, length, count)
     for i in list(range(0, count, 97)) + [count - 1]:
