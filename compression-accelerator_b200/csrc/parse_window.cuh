@@ -41,7 +41,8 @@ __device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return __funnelshi
 
 // ---- input accessors ------------------------------------------------------------------------
 struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
-    static constexpr bool kInPlace = false;
+    static constexpr bool kInPlace = false;          // table in global memory (speculative look-ups, commit in registers)
+    static constexpr bool kInputAhead = false;       // input read in place: keep its lines coming into L1
     const uint8_t* s;
     __device__ __forceinline__ void prefetch(uint32_t) const {}
     __device__ __forceinline__ void touch(uint32_t) const {}
@@ -53,6 +54,7 @@ struct SmemSrc {                         // fragment staged in shared memory (4-
 
 struct GlobalSrc {                       // fragment read in place from global memory
     static constexpr bool kInPlace = true;
+    static constexpr bool kInputAhead = true;
     const uint8_t* g;                    // fragment start (any alignment)
     __device__ __forceinline__ void prefetch(uint32_t pos) const {       // the 128-byte line holding g[pos] -> L1
         asm volatile("prefetch.global.L1 [%0];" ::"l"(g + pos));
@@ -273,6 +275,8 @@ struct WindowParser {
                 s.touch(tq); s.touch(tq + 15u);              // candidates of the next window (tq: table values < len)
                 const uint32_t p2 = pos + 64u;
                 tq = p2 < ip_limit ? (uint32_t)table[hash32(s.ld32(p2), shift)] : 0u;
+            }
+            if constexpr (Src::kInputAhead) {
                 if (lane == 0 && wbase + 256u < len) s.prefetch(wbase + 256u);   // the input itself, two lines ahead
             }
             ek = lane + 4 + ml;                              // lane of ip after taking my copy

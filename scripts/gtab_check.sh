@@ -1,2 +1,2 @@
 #!/bin/bash
-timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
+for b in 1024 2048 4096 8192; do for mode in exact exact_page; do echo "== $b-byte text pages, $mode"; timeout 200 python scripts/run_one.py --batch $b --mib 1024 --reps 3 --mode $mode --decode | tail -2; done; done
