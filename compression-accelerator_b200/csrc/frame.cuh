@@ -433,9 +433,10 @@ __global__ void __launch_bounds__(128, SB_DECODE_MINB) frame_fused_kernel(const 
             uint32_t done = 0, err = 0;
             unsigned long long carry = 0;                                    // hi 24 bits: data chunks, lo 40: output bytes
             for (;;) {
-                const uint32_t hd = s_hop_done;
+                // every lane loads, lane 0's values decide for the warp: the code below is warp-synchronous
+                const uint32_t hd = __shfl_sync(kFull, (uint32_t)s_hop_done, 0);
                 __threadfence_block();
-                const uint32_t avail = s_hopped;
+                const uint32_t avail = __shfl_sync(kFull, (uint32_t)s_hopped, 0);
                 if (avail == done) { if (hd) break; __nanosleep(64); continue; }
                 const uint32_t m = avail - done < 32u ? avail - done : 32u;
                 bool bad = false;
@@ -525,11 +526,11 @@ __global__ void __launch_bounds__(128, SB_DECODE_MINB) frame_fused_kernel(const 
         uint32_t idx = 0;
         if (lane == 0) idx = atomicAdd(&ctl->ticket, 1u);
         idx = __shfl_sync(kFull, idx, 0);
-        for (;;) {
-            uint32_t r = ld_acquire_u32(&ctl->ready);
+        for (;;) {                                   // every lane loads, lane 0's value decides for the warp (the
+            uint32_t r = __shfl_sync(kFull, ld_acquire_u32(&ctl->ready), 0);    // decode below is warp-synchronous)
             if (idx < r) break;
-            if (ld_acquire_u32(&ctl->finished)) {
-                r = ld_acquire_u32(&ctl->ready);
+            if (__shfl_sync(kFull, ld_acquire_u32(&ctl->finished), 0)) {
+                r = __shfl_sync(kFull, ld_acquire_u32(&ctl->ready), 0);
                 if (idx < r) break;
                 return;                                                      // no such chunk: done
             }
