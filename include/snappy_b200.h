@@ -33,6 +33,13 @@ typedef enum {
  * (tests/snappy/snappy.cc:539-671) and is byte-identical to the reference.  FAST is a
  * parallel parse: always a valid Snappy stream, bytes may differ. */
 typedef enum { SNAPPY_B200_EXACT = 0, SNAPPY_B200_FAST = 1 } snappy_b200_mode;
+/* The `mode` arguments also accept diagnostic selectors that force ONE of the exact engines (tests, A/B
+ * runs; every one of them produces the reference's bytes; not part of the contract and subject to change):
+ *   2 serial warp parser, 3 single-warp window parser, 4 pipelined parser with the fragment staged by TMA,
+ *   5 lane parser (one thread per fragment, fat table entries in global memory),
+ *   6 pipelined parser (one CTA per fragment, table in shared memory),
+ *   7 window parser with its table in global memory (one warp per fragment).
+ * SNAPPY_B200_EXACT picks among 5, 6, 7 (and the page / small-buffer kernels of the batch entry) by shape. */
 
 typedef struct snappy_b200_ctx snappy_b200_ctx; /* owns one CUDA stream + device/pinned scratch */
 
