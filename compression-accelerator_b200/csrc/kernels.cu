@@ -540,6 +540,9 @@ cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_table
     if (p.n_jobs == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
     if (e != cudaSuccess) return e;
+    // (Capping the residency of concurrent launches -- the host entry's chunks -- at 28 CTAs per SM with unused
+    // dynamic shared memory was measured: 24.1 -> 45.9 ms per GiB.  Any shared-memory request shrinks the L1
+    // carve-out, and this kernel lives on L1 capacity.)
     parse_gtab_kernel<<<p.n_jobs < n_tables ? p.n_jobs : n_tables, 32, 0, st>>>(p, reinterpret_cast<uint16_t*>(tables), ticket);
     if (launches) ++*launches;
     return cudaGetLastError();
