@@ -540,9 +540,10 @@ cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_table
     if (p.n_jobs == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
     if (e != cudaSuccess) return e;
-    // (Capping the residency of concurrent launches -- the host entry's chunks -- at 28 CTAs per SM with unused
-    // dynamic shared memory was measured: 24.1 -> 45.9 ms per GiB.  Any shared-memory request shrinks the L1
-    // carve-out, and this kernel lives on L1 capacity.)
+    // Leave the shared-memory / L1 split to the driver's default for this kernel.  Measured, ms per GiB of text:
+    // default 24.1; 7-10 KB of unused dynamic shared memory per CTA (tried as a residency cap for the host
+    // entry's concurrent chunk launches) 45.9; cudaSharedmemCarveoutMaxL1 as the preferred carve-out 44.1.  Both
+    // departures from the default double the time; the mechanism was not established.
     parse_gtab_kernel<<<p.n_jobs < n_tables ? p.n_jobs : n_tables, 32, 0, st>>>(p, reinterpret_cast<uint16_t*>(tables), ticket);
     if (launches) ++*launches;
     return cudaGetLastError();
