@@ -540,10 +540,12 @@ cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_table
     if (p.n_jobs == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
     if (e != cudaSuccess) return e;
-    // Leave the shared-memory / L1 split to the driver's default for this kernel.  Measured, ms per GiB of text:
-    // default 24.1; 7-10 KB of unused dynamic shared memory per CTA (tried as a residency cap for the host
-    // entry's concurrent chunk launches) 45.9; cudaSharedmemCarveoutMaxL1 as the preferred carve-out 44.1.  Both
-    // departures from the default double the time; the mechanism was not established.
+    // Leave the shared-memory / L1 split to the driver's default for this kernel.  Measured, ms per GiB of text, by
+    // preferred carve-out: default 24.2; 0 % (MaxL1) 44.0 and 5 % 29.7 -- every CTA reserves 1 KB of shared memory
+    // for the system, so one-warp CTAs run short of it and too few are resident; 15 % 24.2, 30 % 24.3, 50 % 24.5;
+    // 75 % 27.7 and 100 % 46.9 -- the L1 gets too small (the same with 7-10 KB of unused dynamic shared memory per
+    // CTA, tried as a residency cap for the host entry's concurrent launches: 45.9).  Two or four warps per CTA
+    // (a smaller reservation, more L1): 24.2, no change.
     parse_gtab_kernel<<<p.n_jobs < n_tables ? p.n_jobs : n_tables, 32, 0, st>>>(p, reinterpret_cast<uint16_t*>(tables), ticket);
     if (launches) ++*launches;
     return cudaGetLastError();
