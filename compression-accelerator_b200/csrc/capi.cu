@@ -134,15 +134,22 @@ snappy_b200_status default_ctx(snappy_b200_ctx** out) {
 // side by side on disjoint fragment ranges was measured and lost (22.1 ms per GiB: the pipelined CTAs
 // need the maximum shared-memory carve-out, which leaves the lane parser 28 KB of L1).
 constexpr int kModeLane = 5, kModePipe = 6, kModeGtab = 7;
-constexpr size_t kLanePoolMaxBytes = 20ull << 30;
+// Cap of the lane parser's table pool: calls that need more run in waves (lane_parse_all).  20 GiB by default;
+// SNAPPY_B200_LANE_POOL_MIB lowers it (tests force waves on small streams with it).
+inline size_t lane_pool_max() {
+    static const size_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_POOL_MIB"); return e ? (size_t)atol(e) << 20 : (size_t)20 << 30; }();
+    return v;
+}
 inline uint32_t lane_min_frags() {
     static const uint32_t v = [] { const char* e = getenv("SNAPPY_B200_LANE_MIN_FRAGS"); return e ? (uint32_t)atol(e) : 13312u; }();
     return v;
 }
 inline bool lane_chosen(int mode, uint64_t n_jobs, uint32_t job_len) {
     if (mode == kModeLane) return true;
+    // calls whose tables exceed the pool cap (streams over 2.5 GiB) go to the global-table parser: the lane parser
+    // in waves was measured slower (3 GiB of text: two waves 78.2 ms, global-table parser 72.1 ms)
     return mode == SNAPPY_B200_EXACT && job_len == sb::kBlock && n_jobs >= lane_min_frags() &&
-           sb::lane_pool_bytes(n_jobs, job_len) <= kLanePoolMaxBytes;
+           sb::lane_pool_bytes(n_jobs, job_len) <= lane_pool_max();
 }
 inline int kernel_mode(int mode) { return mode == kModePipe ? (int)SNAPPY_B200_EXACT : mode; }
 
@@ -189,9 +196,14 @@ snappy_b200_status lane_begin(snappy_b200_ctx* c, uint64_t n_jobs, uint32_t job_
 
 // Parse + sizes of all jobs of `p` on c->stream, in waves if the pool cap is smaller than the batch.
 snappy_b200_status lane_parse_all(snappy_b200_ctx* c, const sb::JobParams& p) {
+    if (p.n_jobs == 0) return SNAPPY_B200_OK;
     const size_t per_job = sb::lane_pool_bytes(1, p.job_len);
-    uint64_t per_wave = kLanePoolMaxBytes / per_job;
-    if (per_wave > p.n_jobs) per_wave = p.n_jobs;
+    uint64_t per_wave = lane_pool_max() / per_job;
+    if (per_wave == 0) per_wave = 1;
+    {   // equal waves: a short last wave would pay the kernel's latency floor for a handful of fragments
+        const uint64_t waves = (p.n_jobs + per_wave - 1) / per_wave;
+        per_wave = (p.n_jobs + waves - 1) / waves;
+    }
     for (uint64_t j0 = 0; j0 < p.n_jobs; j0 += per_wave) {
         sb::JobParams q = p;
         q.in += j0 * p.in_stride;

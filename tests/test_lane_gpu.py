@@ -115,3 +115,34 @@ def test_large_stream_every_exact_engine(ctx, oracle):
         ctx.sync()
         total = int(out_n.item())
         assert hashlib.sha256(dst[:total].cpu().numpy().tobytes()).hexdigest() == want, mode
+
+
+_WAVES = r"""
+import hashlib, os, sys
+sys.path.insert(0, os.path.join(os.getcwd(), "tests"))
+import corpus, oracle_lib
+import __graft_entry__ as g
+pkg = g.load_package()
+ctx = pkg.Context(0)
+orc = oracle_lib.checker()
+for n in (65536 * 100 + 777, 65536 * 33, 65536 * 32 + 1, 65536 * 31 + 65535):
+    data = corpus.repeat_to(corpus.fixture("all-mtg-cards.txt"), n).tobytes()
+    want = orc.compress(data)
+    assert ctx.compress(data, mode="exact_lane") == want, n
+assert ctx.compress(b"", mode="exact_lane") == orc.compress(b"")
+print("waves: ok")
+"""
+
+
+def test_lane_waves_fresh_process():
+    """Calls whose tables exceed the pool cap run in equal waves over one pool (capi.cu lane_parse_all).  The cap is
+    20 GiB (only the forced mode gets there: exact mode sends such streams to the global-table parser); here it is
+    lowered to 16 MiB = 32 fragments a wave, so that a 6.5 MiB stream takes four waves."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, SNAPPY_B200_LANE_POOL_MIB="16")
+    r = subprocess.run([sys.executable, "-c", _WAVES], capture_output=True, text=True, timeout=600, cwd=root, env=env)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
+    assert "waves: ok" in r.stdout
