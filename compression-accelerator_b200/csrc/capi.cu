@@ -625,7 +625,7 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
         return fail(SNAPPY_B200_BUFFER_TOO_SMALL, "out_stride < max_compressed_length(len)");
     if (bind(c) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
     if (count == 0) return SNAPPY_B200_OK;
-    // exact mode, buffers up to 512 bytes: one thread per buffer, parse and emission fused (parse_tiny.cuh)
+    // exact mode, buffers up to 256 bytes: one thread per buffer, parse and emission fused (parse_tiny.cuh)
     static const bool tiny_on = [] { const char* e = getenv("SNAPPY_B200_TINY"); return !e || atoi(e) != 0; }();
     const bool tiny = mode == SNAPPY_B200_EXACT && tiny_on && sb::tiny_takes((uint32_t)len);
     if (!tiny) {
@@ -650,6 +650,11 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     const bool lane = lane_chosen(mode, count, (uint32_t)len);
     const bool gtab = gtab_chosen(mode, count, (uint32_t)len);
     if (gtab && gtab_reserve(c, 1, sb::gtab_tables()) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
+    // buffers of the page parser: the parsing warp writes the elements too (kernels.cu warp_emit_job).  Text, GB/s
+    // with / without: 600 B 81.8 / 52.8, 1,000 B 85.3 / 63.0, 2,000 B 93.6 / 78.6, 4 KiB 75.3 / 71.2.
+    static const size_t fuse_max = [] { const char* e = getenv("SNAPPY_B200_FUSE_EMIT_MAX"); return e ? (size_t)atol(e) : (size_t)8192; }();
+    const bool fused = mode == SNAPPY_B200_EXACT && !tiny && !lane && !gtab && len <= fuse_max && sb::page_parser_takes((uint32_t)len);
+    p.fuse_emit = fused ? 1u : 0u;
     CU(cudaEventRecord(c->evp0, c->stream));
     if (tiny) {
         CU(sb::launch_tiny(p, c->stream, &c->launches));
@@ -664,8 +669,10 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     else CU(sb::launch_parse(p, kernel_mode(mode), c->stream, &c->launches));
     CU(cudaEventRecord(c->evp1, c->stream));
     if (debug_check(c, p) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));
-    CU(sb::launch_emit(p, c->stream, &c->launches));
+    if (!fused) {
+        if (!lane) CU(sb::launch_size(p, c->stream, &c->launches));
+        CU(sb::launch_emit(p, c->stream, &c->launches));
+    }
     CU(cudaEventRecord(c->evp2, c->stream));
     c->staged = true;
     return SNAPPY_B200_OK;

@@ -72,12 +72,71 @@ __device__ __noinline__ void emit_one_literal(uint8_t* dst, uint32_t with_header
     if (lane == 0) { *size_slot = op; *nseq_slot = kSeqEmitted; }
 }
 
+// Batch path, short jobs: the warp that parsed the job turns its sequences into elements right away (what
+// size_kernel + emit_kernel do with a warp / a 256-thread CTA per job in two more launches: for 1,000-byte text
+// buffers those took 5.8 ms per GiB next to 11.4 ms of parsing, most of it CTA launch rate).  32 sequences a round:
+// a warp scan of input / output lengths gives every lane its element's place (snappy.cc:337-431 for the bytes);
+// literals come from the copy staged in shared memory, the long ones written by the whole warp.
+constexpr uint32_t kLaneLiteral = 16;
+__device__ __noinline__ void warp_emit_job(uint8_t* out, uint32_t with_header, uint32_t* size_slot, uint32_t* nseq_slot,
+                                           uint32_t len, const uint8_t* s_in, const seq_t* q, uint32_t n, int lane) {
+    unsigned long long carry = 0;                            // hi32 = input position, lo32 = output position
+    if (with_header) {
+        carry = varint32_len(len);
+        if (lane == 0) put_varint32(out, len);
+    }
+    __syncwarp();                                            // the sequences were written by other lanes
+    for (uint32_t base = 0; base < n; base += 32) {
+        const uint32_t i = base + lane;
+        const seq_t sq = i < n ? q[i] : 0ull;
+        const uint32_t lit = seq_lit(sq), clen = seq_len(sq), off = seq_off(sq);
+        const uint32_t lh = lit ? literal_header_size(lit) : 0;
+        const uint32_t osz = lh + lit + (clen ? copy_encoded_size(off, clen) : 0);
+        const unsigned long long v = ((unsigned long long)(lit + clen) << 32) | osz;
+        unsigned long long x = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long y = __shfl_up_sync(kFull, x, d);
+            if (lane >= d) x += y;
+        }
+        const unsigned long long excl = carry + x - v;
+        const uint32_t ipos = (uint32_t)(excl >> 32);
+        uint32_t op = (uint32_t)excl;
+        const bool by_warp = lit > kLaneLiteral;
+        if (lit && !by_warp) {                               // EmitLiteral, tag only (lit <= 60)
+            out[op] = (uint8_t)((lit - 1) << 2);
+            for (uint32_t b = 0; b < lit; ++b) out[op + 1 + b] = s_in[ipos + b];
+        }
+        op += lh + lit;
+        if (clen) {                                          // EmitCopy
+            uint32_t rem = clen;
+            if (rem >= 12) {
+                while (rem >= 68) { op += put_copy_le64(out + op, off, 64, false); rem -= 64; }
+                if (rem > 64) { op += put_copy_le64(out + op, off, 60, false); rem -= 60; }
+            }
+            put_copy_le64(out + op, off, rem, rem < 12);
+        }
+        uint32_t longs = __ballot_sync(kFull, by_warp);
+        while (longs) {
+            const int k = __ffs(longs) - 1;
+            longs &= longs - 1;
+            warp_emit_literal(out, __shfl_sync(kFull, (uint32_t)excl, k), s_in, __shfl_sync(kFull, ipos, k),
+                              __shfl_sync(kFull, lit, k), lane);
+        }
+        carry = __shfl_sync(kFull, excl + v, 31);
+    }
+    if (lane == 0) { *size_slot = (uint32_t)carry; *nseq_slot = kSeqEmitted; }
+}
+
 // One warp (one CTA) per job.  Packing several page-sized jobs into one CTA to spread the per-CTA
 // shared-memory reservation (18 instead of 17 4 KiB pages per SM) was measured and lost: a CTA's
 // resources return only when its slowest job ends, and the kernel compiled for more than one warp per
 // CTA ran 12 % slower per page (85 -> 75-77 GB/s on 4 KiB text pages).
-template <bool kWindow>
-__global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
+// kCtas = 32 caps the kernel at 64 registers (71 otherwise): 32 instead of 28 jobs per SM where shared memory leaves
+// room for them -- buffers up to 2 KiB (text, GB/s: 300 B 72.6 -> 75.8, 1,000 B 85.5 -> 88.7, 2,000 B 93.8 -> 97.1;
+// 4 KiB pages fit 17 per SM either way and lose 3 % on incompressible data, so they keep the uncapped build).
+template <bool kWindow, int kCtas = 1>
+__global__ void __launch_bounds__(32, kCtas) parse_kernel(JobParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int lane = threadIdx.x;
     const uint32_t job = blockIdx.x;
@@ -97,6 +156,11 @@ __global__ void __launch_bounds__(32) parse_kernel(JobParams p) {
     // does not read it from DRAM a second time (snappy.cc:1006-1009 preamble, :337-378 EmitLiteral).
     if (kWindow && one_literal && !p.offsets && !p.sparse) {
         emit_one_literal(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len, s_in, lane);
+        return;
+    }
+    if (kWindow && p.fuse_emit) {
+        warp_emit_job(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len, s_in,
+                      out.seqs, out.n, lane);
         return;
     }
     if (lane == 0) p.nseq[job] = out.n;
@@ -462,6 +526,8 @@ cudaError_t kernels_init() {
     return cudaMemcpyToSymbol(g_crc_ops, &ops, sizeof(ops));
 }
 
+bool page_parser_takes(uint32_t job_len) { return job_len <= SB_PIPE_MIN_LEN; }
+
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
                          unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;
@@ -473,6 +539,7 @@ cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st,
         parse_pipe_kernel<true><<<p.n_jobs, 32 * (1 + PipeCfg<true>::P), pipe_smem_bytes<true>(p.job_len), st>>>(p);
     else if (mode == 4)
         parse_pipe_kernel<false><<<p.n_jobs, 32 * (1 + PipeCfg<false>::P), pipe_smem_bytes<false>(p.job_len), st>>>(p);
+    else if (p.job_len <= 2048) parse_kernel<true, 32><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     else parse_kernel<true><<<p.n_jobs, 32, parse_smem_bytes(p.job_len), st>>>(p);
     if (launches) ++*launches;
     return cudaGetLastError();
@@ -552,7 +619,13 @@ cudaError_t launch_parse_gtab(const JobParams& p, void* tables, uint32_t n_table
 }
 
 // ---- small buffers: one thread per buffer, parse + emission fused (parse_tiny.cuh) -------------------
-bool tiny_takes(uint32_t job_len) { return job_len <= tiny::kMaxLen; }
+bool tiny_takes(uint32_t job_len) {
+    static const uint32_t max_len = [] {
+        const int v = env_int("SNAPPY_B200_TINY_MAX", (int)tiny::kMaxLen);
+        return v < 0 ? 0u : (uint32_t)v > tiny::kMaxLenLimit ? tiny::kMaxLenLimit : (uint32_t)v;
+    }();
+    return job_len <= max_len;
+}
 
 cudaError_t launch_tiny(const JobParams& p, cudaStream_t st, unsigned long long* launches) {
     if (p.n_jobs == 0) return cudaSuccess;

@@ -49,9 +49,12 @@ struct JobParams {
     uint64_t out_stride;
     const unsigned long long* offsets;
     unsigned int* err = nullptr;   // the context's error word (mapped host memory): a parser watchdog stores 1 here
+    uint32_t fuse_emit = 0;        // batch path, page parser: the warp that parsed a job writes its elements too
+                                   // (sizes[j] final, nseq[j] = kSeqEmitted; no size / emit launch follows)
 };
 
 cudaError_t launch_parse(const JobParams& p, int mode, cudaStream_t st, unsigned long long* launches);
+bool page_parser_takes(uint32_t job_len);   // exact mode: jobs of this length go to the one-warp page parser (parse_kernel<true>)
 
 // Lane parser (parse_lane.cuh): one thread per job, all jobs in flight, "fat" hash-table entries in a
 // pool in global memory that is never cleared between launches (entries carry the launch's epoch).

@@ -1,9 +1,9 @@
 // parse_tiny.cuh -- small buffers of a batch (the reference's own benchmark shape: 10 .. 2,000-byte
-// buffers, benchmark/hw_results.csv, DataGenerator.scala:27; this kernel takes those up to 512 bytes): ONE THREAD compresses one buffer from
+// buffers, benchmark/hw_results.csv, DataGenerator.scala:27; this kernel takes those up to 256 bytes): ONE THREAD compresses one buffer from
 // start to finish -- parse and emission fused, no sequence list, no size / emit pass.
 //
 // Why: a warp or a CTA per 100-byte buffer is launch-bound (2.6 ns per buffer whatever its size: 107 M
-// CTAs for 1 GiB of 10-byte buffers, and a 256-thread emit CTA per buffer behind it).  A buffer of up to
+// CTAs for 1 GiB of 10-byte buffers).  A buffer of up to
 // 512 bytes needs a table of at most 512 uint16 entries (tests/snappy/snappy.cc:445-456), so 200-256 of
 // them fit an SM's shared memory at once and each is a short serial chain; the lanes of a warp run
 // different buffers in lock step.
@@ -30,10 +30,13 @@ namespace tiny {
 
 constexpr uint32_t kMul = 0x1e35a7bdu;      // tests/snappy/snappy.cc:92
 constexpr uint32_t kMargin = 15;            // snappy.cc:556 kInputMarginBytes
-constexpr uint32_t kMaxLen = 512;           // buffers this kernel takes.  Measured against the warp-per-buffer parser
-                                            // (GB/s, random / text / constant buffers): 100 B 92/90/431 vs 25/21/35,
-                                            // 500 B 83/65/220 vs 88/40/155, 1000 B 78/45/157 vs 160/57/289 -- beyond
-                                            // ~500 bytes a warp's 32-position windows beat one serial thread.
+constexpr uint32_t kMaxLen = 256;           // buffers this kernel takes (SNAPPY_B200_TINY_MAX overrides, up to 512).
+                                            // Measured against the warp-per-buffer parser, which also writes its
+                                            // elements itself (GB/s on 512 MiB of text / random / constant buffers):
+                                            // 100 B 72/91/431 vs 54/73/110, 200 B 62/94/430 vs 64/123/212, 300 B
+                                            // 39/76/221 vs 72/186/285, 512 B 34/73/301 vs 78/292/561 -- beyond ~250
+                                            // bytes a warp's 32-position windows beat one serial thread.
+constexpr uint32_t kMaxLenLimit = 512;
 
 SB_THD uint32_t entries_for(uint32_t len) {                     // snappy.cc:445-456
     uint32_t e = 256;

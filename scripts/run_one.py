@@ -41,9 +41,9 @@ def main():
         for _ in range(a.reps):
             dst, ostride, sizes = ctx.compress_batch_device(src, a.batch, a.batch, count, mode=a.mode)
             ctx.sync()
-            ms = ctx.stage_ms(0)
-            print("batch %d x %d B: parse %.3f ms  %.2f GB/s in, out/in %.4f" % (
-                count, a.batch, ms, count * a.batch / ms / 1e6, float(sizes.sum().item()) / (count * a.batch)))
+            ms, ms1 = ctx.stage_ms(0), ctx.stage_ms(1)
+            print("batch %d x %d B: parse %.3f ms  size+emit %.3f ms  %.2f GB/s in, out/in %.4f" % (
+                count, a.batch, ms, ms1, count * a.batch / (ms + ms1) / 1e6, float(sizes.sum().item()) / (count * a.batch)))
         if a.decode:
             import time
             back, lens = ctx.uncompress_batch_device(dst, ostride, sizes, count, a.batch)

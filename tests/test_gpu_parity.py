@@ -102,7 +102,7 @@ def test_batch_pages_exact(ctx, oracle):
         assert bytes(out[i * ostride:i * ostride + 2]) == b"\x80\x20"
 
 
-@pytest.mark.parametrize("length", [1, 14, 15, 100, 255, 256, 1000, 2048, 4096, 5000, 8192, 8193, 12000, 16384, 50000,
+@pytest.mark.parametrize("length", [1, 14, 15, 100, 255, 256, 257, 300, 512, 1000, 2048, 4096, 5000, 8192, 8193, 12000, 16384, 50000,
                                     65536])
 def test_batch_size_sweep(ctx, oracle, length):
     text = corpus.fixture("alice29.txt")
@@ -132,6 +132,50 @@ def test_batch_incompressible_pages_emitted_by_the_parser(ctx, oracle, length):
     out, ostride, sizes = ctx.compress_batch(buf, length, stride, count)
     for i in range(count):
         want = oracle.compress(bytes(buf[i * stride:i * stride + length]))
+        assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
+
+
+@pytest.mark.parametrize("length", [513, 600, 777, 1000, 1500, 2000, 2048, 3000, 4096, 6000, 8192])
+def test_batch_short_buffers_emitted_by_the_parsing_warp(ctx, oracle, length):
+    """Exact mode, buffers of 513 .. 2,048 bytes: the warp that parsed a buffer also writes its elements
+    (kernels.cu warp_emit_job), 32 sequences a round -- no size / emit launch.  Mixed batch: text, runs (copies of
+    68 bytes and more, split as EmitCopy does), literals of 1 .. 16 bytes (written by their lane), 17 .. 60,
+    61 .. 256 and longer (written by the whole warp, 1-, 2- and 3-byte tags), more than 32 sequences per buffer,
+    a ragged stride; every stream against the oracle.  With 96 buffers, 2,049 and 3,000 bytes are fused as well
+    (the global-table parser takes over only from 1,792 buffers of more than 4 KiB)."""
+    count = 96
+    stride = length + 7
+    rng = np.random.default_rng(length)
+    txt = np.frombuffer((corpus.fixture("all-mtg-cards.txt"))[5000:5000 + stride * count], dtype=np.uint8)
+    buf = txt.copy()
+    for i in range(count):
+        b = buf[i * stride:(i + 1) * stride]
+        k = i % 8
+        if k == 1:                                            # random ASCII with planted repeats: literals of many lengths
+            b[:] = corpus.random_ascii(stride, i)
+            pos = 0
+            for gap in (1, 5, 16, 17, 40, 60, 61, 100, 256, 257, 300):
+                pos += gap + 8
+                if pos + 8 < length:
+                    b[pos:pos + 8] = b[0:8]
+        elif k == 2:
+            b[:] = 97                                         # one run: a single long copy
+        elif k == 3:
+            b[:] = np.tile(rng.integers(0, 256, 70, dtype=np.uint8), stride // 70 + 1)[:stride]   # period 70
+        elif k == 4:
+            b[:] = rng.integers(0, 256, stride, dtype=np.uint8)                                   # one literal
+        elif k == 5:
+            b[:] = np.tile(np.frombuffer(b"abcdefgh", dtype=np.uint8), stride // 8 + 1)[:stride]
+            b[length // 2:length // 2 + 200] = rng.integers(0, 256, 200, dtype=np.uint8)
+    src = buf[:(count - 1) * stride + length].copy()
+    import torch
+    dsrc = torch.from_numpy(src).cuda()
+    dst, ostride, sizes = ctx.compress_batch_device(dsrc, length, stride, count)
+    ctx.sync()
+    out = dst.cpu().numpy()
+    sizes = sizes.cpu().numpy()
+    for i in range(count):
+        want = oracle.compress(bytes(src[i * stride:i * stride + length]))
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
 
 
