@@ -240,13 +240,14 @@ class Context:
     def compress(self, data, mode="exact") -> bytes:
         """snappy::Compress(input, n, &output) (tests/swcompression.cc:45): host bytes in, the
         compressed stream out."""
+        import numpy as np
         n = len(data)
         cap = max_compressed_length(n)
-        out = C.create_string_buffer(cap + 16)
+        out = np.empty(cap + 16, dtype=np.uint8)             # not zero-filled, and only the stream is copied out
         out_n = C.c_size_t(0)
         src = data if isinstance(data, bytes) else bytes(data)
-        _check(lib().snappy_b200_compress(self._h, src, n, out, cap, C.byref(out_n), _MODES[mode]))
-        return out.raw[:out_n.value]
+        _check(lib().snappy_b200_compress(self._h, src, n, out.ctypes.data, cap, C.byref(out_n), _MODES[mode]))
+        return out[:out_n.value].tobytes()
 
     def compress_into(self, src_addr: int, n: int, dst_addr: int, dst_cap: int, mode="exact") -> int:
         """Raw-pointer flavour (pinned or pageable host memory); returns the stream length."""
@@ -272,10 +273,11 @@ class Context:
         raises SnappyB200Error(INVALID_INPUT) for a malformed stream."""
         n = C.c_size_t(0)
         _check(lib().snappy_b200_uncompressed_length(data, len(data), C.byref(n)))
-        out = C.create_string_buffer(n.value + 16)
+        import numpy as np
+        out = np.empty(n.value + 16, dtype=np.uint8)
         got = C.c_size_t(0)
-        _check(lib().snappy_b200_uncompress(self._h, data, len(data), out, n.value, C.byref(got)))
-        return out.raw[:got.value]
+        _check(lib().snappy_b200_uncompress(self._h, data, len(data), out.ctypes.data, n.value, C.byref(got)))
+        return out[:got.value].tobytes()
 
     def uncompress_device(self, src, n, dst, out_n):
         """Decode the n-byte raw stream in device tensor `src` into `dst`; asynchronous.  out_n (a
