@@ -650,10 +650,13 @@ snappy_b200_status snappy_b200_compress_batch_device(snappy_b200_ctx* c, const v
     const bool lane = lane_chosen(mode, count, (uint32_t)len);
     const bool gtab = gtab_chosen(mode, count, (uint32_t)len);
     if (gtab && gtab_reserve(c, 1, sb::gtab_tables()) != SNAPPY_B200_OK) return SNAPPY_B200_CUDA_ERROR;
-    // buffers of the page parser: the parsing warp writes the elements too (kernels.cu warp_emit_job).  Text, GB/s
-    // with / without: 600 B 81.8 / 52.8, 1,000 B 85.3 / 63.0, 2,000 B 93.6 / 78.6, 4 KiB 75.3 / 71.2.
+    // buffers of the page parser and of the global-table parser: the parsing warp writes the elements too
+    // (kernels.cu warp_emit_job).  Text, GB/s with / without: 600 B 81.8 / 52.8, 1,000 B 85.3 / 63.0, 2,000 B 93.6 /
+    // 78.6, 4 KiB 75.3 / 71.2.
     static const size_t fuse_max = [] { const char* e = getenv("SNAPPY_B200_FUSE_EMIT_MAX"); return e ? (size_t)atol(e) : (size_t)8192; }();
-    const bool fused = mode == SNAPPY_B200_EXACT && !tiny && !lane && !gtab && len <= fuse_max && sb::page_parser_takes((uint32_t)len);
+    static const size_t fuse_gtab_max = [] { const char* e = getenv("SNAPPY_B200_FUSE_EMIT_GTAB_MAX"); return e ? (size_t)atol(e) : (size_t)32768; }();
+    const bool fused = (mode == SNAPPY_B200_EXACT || mode == kModeGtab) && !tiny && !lane &&
+                       (gtab ? len <= fuse_gtab_max : len <= fuse_max && sb::page_parser_takes((uint32_t)len));
     p.fuse_emit = fused ? 1u : 0u;
     CU(cudaEventRecord(c->evp0, c->stream));
     if (tiny) {

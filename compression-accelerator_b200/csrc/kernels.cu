@@ -77,7 +77,10 @@ __device__ __noinline__ void emit_one_literal(uint8_t* dst, uint32_t with_header
 // buffers those took 5.8 ms per GiB next to 11.4 ms of parsing, most of it CTA launch rate).  32 sequences a round:
 // a warp scan of input / output lengths gives every lane its element's place (snappy.cc:337-431 for the bytes);
 // literals come from the copy staged in shared memory, the long ones written by the whole warp.
+// kSmem: `s_in` is the copy staged in shared memory (4-byte aligned, padded); otherwise the buffer itself in global
+// memory, any alignment (the global-table parser reads its input in place).
 constexpr uint32_t kLaneLiteral = 16;
+template <bool kSmem>
 __device__ __noinline__ void warp_emit_job(uint8_t* out, uint32_t with_header, uint32_t* size_slot, uint32_t* nseq_slot,
                                            uint32_t len, const uint8_t* s_in, const seq_t* q, uint32_t n, int lane) {
     unsigned long long carry = 0;                            // hi32 = input position, lo32 = output position
@@ -86,9 +89,10 @@ __device__ __noinline__ void warp_emit_job(uint8_t* out, uint32_t with_header, u
         if (lane == 0) put_varint32(out, len);
     }
     __syncwarp();                                            // the sequences were written by other lanes
+    seq_t sq_next = (uint32_t)lane < n ? q[lane] : 0ull;     // one round ahead: the list comes back from L2
     for (uint32_t base = 0; base < n; base += 32) {
-        const uint32_t i = base + lane;
-        const seq_t sq = i < n ? q[i] : 0ull;
+        const seq_t sq = sq_next;
+        sq_next = base + 32 + lane < n ? q[base + 32 + lane] : 0ull;
         const uint32_t lit = seq_lit(sq), clen = seq_len(sq), off = seq_off(sq);
         const uint32_t lh = lit ? literal_header_size(lit) : 0;
         const uint32_t osz = lh + lit + (clen ? copy_encoded_size(off, clen) : 0);
@@ -120,8 +124,19 @@ __device__ __noinline__ void warp_emit_job(uint8_t* out, uint32_t with_header, u
         while (longs) {
             const int k = __ffs(longs) - 1;
             longs &= longs - 1;
-            warp_emit_literal(out, __shfl_sync(kFull, (uint32_t)excl, k), s_in, __shfl_sync(kFull, ipos, k),
-                              __shfl_sync(kFull, lit, k), lane);
+            const uint32_t dst = __shfl_sync(kFull, (uint32_t)excl, k), src = __shfl_sync(kFull, ipos, k);
+            const uint32_t L = __shfl_sync(kFull, lit, k);
+            if constexpr (kSmem) {
+                warp_emit_literal(out, dst, s_in, src, L, lane);
+            } else {                                         // EmitLiteral tag (snappy.cc:337-378), then the bytes
+                const uint32_t m = L - 1, lhk = literal_header_size(L);
+                if (lane == 0) {
+                    if (m < 60) out[dst] = (uint8_t)(m << 2);
+                    else if (m < 256) { out[dst] = 60u << 2; out[dst + 1] = (uint8_t)m; }
+                    else { out[dst] = 61u << 2; out[dst + 1] = (uint8_t)m; out[dst + 2] = (uint8_t)(m >> 8); }
+                }
+                block_copy(out + dst + lhk, s_in + src, L, (uint32_t)lane, 32u);
+            }
         }
         carry = __shfl_sync(kFull, excl + v, 31);
     }
@@ -159,8 +174,8 @@ __global__ void __launch_bounds__(32, kCtas) parse_kernel(JobParams p) {
         return;
     }
     if (kWindow && p.fuse_emit) {
-        warp_emit_job(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len, s_in,
-                      out.seqs, out.n, lane);
+        warp_emit_job<true>(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len, s_in,
+                            out.seqs, out.n, lane);
         return;
     }
     if (lane == 0) p.nseq[job] = out.n;
@@ -194,6 +209,12 @@ __global__ void __launch_bounds__(32) parse_gtab_kernel(JobParams p, uint16_t* p
         GlobalSrc src;
         src.g = p.in + (uint64_t)job * p.in_stride;
         parse_fragment_window(src, len, table, shift, out, lane);
+        if (p.fuse_emit) {                                   // batch path: this warp writes the buffer's elements too
+            warp_emit_job<false>(p.out + (uint64_t)job * p.out_stride, p.with_header, p.sizes + job, p.nseq + job, len,
+                                 src.g, out.seqs, out.n, lane);
+            __syncwarp();
+            continue;
+        }
         if (lane == 0) p.nseq[job] = out.n;
         __syncwarp();
     }

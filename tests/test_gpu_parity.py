@@ -135,18 +135,20 @@ def test_batch_incompressible_pages_emitted_by_the_parser(ctx, oracle, length):
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
 
 
-@pytest.mark.parametrize("length", [513, 600, 777, 1000, 1500, 2000, 2048, 3000, 4096, 6000, 8192])
-def test_batch_short_buffers_emitted_by_the_parsing_warp(ctx, oracle, length):
+@pytest.mark.parametrize("length,count", [(513, 96), (600, 96), (777, 96), (1000, 96), (1500, 96), (2000, 96), (2048, 96),
+                                          (3000, 96), (4096, 96), (6000, 96), (8192, 96),
+                                          (4100, 1800), (5000, 1800), (20000, 1800), (50000, 1800)])
+def test_batch_short_buffers_emitted_by_the_parsing_warp(ctx, oracle, length, count):
     """Exact mode, buffers of 513 .. 2,048 bytes: the warp that parsed a buffer also writes its elements
     (kernels.cu warp_emit_job), 32 sequences a round -- no size / emit launch.  Mixed batch: text, runs (copies of
     68 bytes and more, split as EmitCopy does), literals of 1 .. 16 bytes (written by their lane), 17 .. 60,
     61 .. 256 and longer (written by the whole warp, 1-, 2- and 3-byte tags), more than 32 sequences per buffer,
-    a ragged stride; every stream against the oracle.  With 96 buffers, 2,049 and 3,000 bytes are fused as well
-    (the global-table parser takes over only from 1,792 buffers of more than 4 KiB)."""
-    count = 96
+    a ragged stride; every stream against the oracle.  The cases with 1,800 buffers of more than 4 KiB go through the
+    global-table parser, whose warps emit from the buffer in place (global memory) instead of a staged copy."""
     stride = length + 7
     rng = np.random.default_rng(length)
-    txt = np.frombuffer((corpus.fixture("all-mtg-cards.txt"))[5000:5000 + stride * count], dtype=np.uint8)
+    text = corpus.fixture("all-mtg-cards.txt")
+    txt = np.frombuffer((text * (stride * count // len(text) + 2))[5000:5000 + stride * count], dtype=np.uint8)
     buf = txt.copy()
     for i in range(count):
         b = buf[i * stride:(i + 1) * stride]
@@ -174,7 +176,7 @@ def test_batch_short_buffers_emitted_by_the_parsing_warp(ctx, oracle, length):
     ctx.sync()
     out = dst.cpu().numpy()
     sizes = sizes.cpu().numpy()
-    for i in range(count):
+    for i in (range(count) if count <= 96 else list(range(0, count, 7)) + [count - 1]):
         want = oracle.compress(bytes(src[i * stride:i * stride + length]))
         assert bytes(out[i * ostride:i * ostride + sizes[i]]) == want, i
 
