@@ -128,18 +128,44 @@ __device__ __forceinline__ uint32_t src_match_len(const Src& src, uint32_t a, ui
 // whose successor passes ip_limit (:598); exactly those lanes insert, the highest lane of a slot winning as
 // in serial order.  Returns like the serial scan: true with (ip, cand) of the hit, false when the scan ran
 // off the fragment.
+//
+// The schedule as a table.  skip and the position advance by the same step, so skip - 32 is the distance from
+// the scan's first probe and the whole schedule is ONE sequence of distances, o(0) = 0, o(n+1) = o(n) + 1 +
+// (o(n) >> 5): 267 entries cover a fragment.  Lane k reads o(n0 + k) -- one coalesced load -- instead of
+// stepping through k probes (a 31-iteration loop per lane: 6 % of the page parser's instructions on text, most
+// of them on incompressible data).
+struct SkipSchedule {
+    static constexpr int kN = 320;                           // o(266) = 66,672 > 65,536; n0 + 32 stays inside
+    uint32_t off[kN];
+    constexpr SkipSchedule() : off() {
+        uint32_t o = 0;
+        for (int n = 0; n < kN; ++n) { off[n] = o; o += 1u + (o >> 5); }
+    }
+};
+static __device__ const SkipSchedule g_skip_schedule = SkipSchedule();
+
+// n with o(n) == skip - 32 (skip is always a member: it only ever grows by this rule from 32)
+__device__ __forceinline__ uint32_t skip_schedule_index(uint32_t skip, int lane) {
+    const uint32_t o = skip - 32u;
+    if (o <= 32u) return o;                                  // o(n) = n up to 32
+    uint32_t below = 0;                                      // entries of my ten that are <= o
+#pragma unroll
+    for (int j = 0; j < SkipSchedule::kN / 32; ++j)
+        below += __ldg(&g_skip_schedule.off[lane * (SkipSchedule::kN / 32) + j]) <= o ? 1u : 0u;
+    for (int d = 16; d; d >>= 1) below += __shfl_xor_sync(kFull, below, d);
+    return below - 1u;
+}
+
 template <class Src>
 __device__ __forceinline__ bool src_serial_scan(const Src& src, uint16_t* table, int shift,
                                                 uint32_t ip_limit, uint32_t& ip, uint32_t& skip,
                                                 uint32_t& cand, int lane) {
     const uint32_t lt = (1u << lane) - 1u;
-    for (;;) {
-        uint32_t pos = ip, sk = skip;                        // my probe: the lane-th of the schedule
-#pragma unroll 8
-        for (int j = 0; j < 31; ++j) {
-            const uint32_t st = sk >> 5;
-            if (j < lane) { sk += st; pos += st; }
-        }
+    uint32_t n0 = skip_schedule_index(skip, lane);
+    const uint32_t origin = ip - (skip - 32u);               // where this scan's first probe was
+    for (;; n0 += 32u) {
+        const uint32_t o = __ldg(&g_skip_schedule.off[n0 + lane]);   // my probe: the lane-th from here
+        const uint32_t pos = origin + o, sk = 32u + o;
         const uint32_t step = sk >> 5, nxt = pos + step;     // :590-597 for my probe
         const bool valid = nxt <= ip_limit;                  // :598 (positions grow with the lane: a prefix is valid)
         uint32_t w = 0, h = 0x10000u + (uint32_t)lane;       // invalid lanes: a hash nobody shares
