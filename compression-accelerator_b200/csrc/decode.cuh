@@ -64,10 +64,10 @@ __device__ __forceinline__ void decode_literal(uint8_t* __restrict__ d, const ui
         const uint32_t a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2), a3 = __ldg(q + 3);
         const uint32_t a4 = sh ? __ldg(q + 4) : 0u;
         uint4 v;
-        v.x = __funnelshift_r(a0, a1, sh);
-        v.y = __funnelshift_r(a1, a2, sh);
-        v.z = __funnelshift_r(a2, a3, sh);
-        v.w = __funnelshift_r(a3, a4, sh);
+        v.x = shf_r(a0, a1, sh);
+        v.y = shf_r(a1, a2, sh);
+        v.z = shf_r(a2, a3, sh);
+        v.w = shf_r(a3, a4, sh);
         d4[j] = v;
     }
     const uint32_t done = head + (body << 4);
@@ -189,7 +189,7 @@ constexpr uint32_t kStageOutMax = 8192;          // largest decoded size the sta
 // unaligned 4 bytes from shared memory (the staging areas are padded: reading 3 bytes past is safe)
 __device__ __forceinline__ uint32_t stage_ld32(const uint8_t* s, uint32_t pos) {
     const uint32_t* w = reinterpret_cast<const uint32_t*>(s) + (pos >> 2);
-    return __funnelshift_r(w[0], w[1], (pos & 3u) << 3);
+    return shf_r(w[0], w[1], (pos & 3u) << 3);
 }
 
 __global__ void __launch_bounds__(32 * kStageWarps) decode_staged_kernel(DecodeParams p, uint32_t stage_in,

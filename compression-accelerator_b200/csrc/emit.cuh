@@ -74,10 +74,10 @@ __device__ __forceinline__ void block_copy(uint8_t* __restrict__ d, const uint8_
             uint32_t a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2), a3 = __ldg(q + 3);
             uint32_t a4 = sh ? __ldg(q + 4) : 0u;      // never read past the source when aligned
             uint4 v;
-            v.x = __funnelshift_r(a0, a1, sh);
-            v.y = __funnelshift_r(a1, a2, sh);
-            v.z = __funnelshift_r(a2, a3, sh);
-            v.w = __funnelshift_r(a3, a4, sh);
+            v.x = shf_r(a0, a1, sh);
+            v.y = shf_r(a1, a2, sh);
+            v.z = shf_r(a2, a3, sh);
+            v.w = shf_r(a3, a4, sh);
             d4[j] = v;
         }
     }

@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kCrcThreads) crc32c_chunks_kernel(CrcParams p)
             for (; x < xe; x += 4) {
                 y += 4;
                 const uint32_t hi = sw[crc_stage_word(y)];
-                crc ^= __funnelshift_r(lo, hi, sh);
+                crc ^= shf_r(lo, hi, sh);
                 lo = hi;
                 crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
                 crc = Tl[(crc & 0xffu) << 5] ^ (crc >> 8);
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(32) frame_hop_kernel(const uint8_t* __restrict
         const uintptr_t a0 = (uintptr_t)(src + pos);
         const uint32_t* wp = (const uint32_t*)(a0 & ~(uintptr_t)3);
         const uint32_t w0 = __ldcg(wp), w1 = ((uintptr_t)(wp + 1) < end) ? __ldcg(wp + 1) : 0u;
-        const uint32_t len = __funnelshift_r(w0, w1, (uint32_t)(a0 & 3u) << 3) >> 8;
+        const uint32_t len = shf_r(w0, w1, (uint32_t)(a0 & 3u) << 3) >> 8;
         if (pos + 4 + len > n) { err = 1; break; }
         if (cnt < max_records) { if (lane == 0) t_pos[cnt] = pos; }
         else if (!err) err = 2;                                              // keep counting: the host retries
@@ -289,8 +289,8 @@ __global__ void __launch_bounds__(256) frame_parse_kernel(const uint8_t* __restr
     uint32_t w[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) w[k] = ((uintptr_t)(wp + k) < end) ? __ldg(wp + k) : 0u;
-    const uint32_t d0 = __funnelshift_r(w[0], w[1], sh), d1 = __funnelshift_r(w[1], w[2], sh),
-                   d2 = __funnelshift_r(w[2], w[3], sh), d3 = __funnelshift_r(w[3], w[4], sh);
+    const uint32_t d0 = shf_r(w[0], w[1], sh), d1 = shf_r(w[1], w[2], sh),
+                   d2 = shf_r(w[2], w[3], sh), d3 = shf_r(w[3], w[4], sh);
     const uint32_t type = d0 & 0xffu, len = d0 >> 8;
     bool bad = (i == 0 && type != 0xff);                                     // :20-21
     uint32_t kind = kFrameNotData, plen = 0, ulen = 0;
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(128, SB_DECODE_MINB) frame_fused_kernel(const 
                 const uintptr_t a0 = (uintptr_t)(src + pos);
                 const uint32_t* wp = (const uint32_t*)(a0 & ~(uintptr_t)3);
                 const uint32_t w0 = __ldcg(wp), w1 = ((uintptr_t)(wp + 1) < end) ? __ldcg(wp + 1) : 0u;
-                const uint32_t len = __funnelshift_r(w0, w1, (uint32_t)(a0 & 3u) << 3) >> 8;
+                const uint32_t len = shf_r(w0, w1, (uint32_t)(a0 & 3u) << 3) >> 8;
                 if (pos + 4 + len > n) { err = 1; break; }
                 while (cnt - s_parsed >= kHopRing && !s_abort) __nanosleep(64);   // never laps the parser (it is 32 x faster)
                 if (s_abort) break;
@@ -450,8 +450,8 @@ __global__ void __launch_bounds__(128, SB_DECODE_MINB) frame_fused_kernel(const 
                     uint32_t w[5];
 #pragma unroll
                     for (int k = 0; k < 5; ++k) w[k] = ((uintptr_t)(wp + k) < end) ? __ldcg(wp + k) : 0u;
-                    const uint32_t d0 = __funnelshift_r(w[0], w[1], sh), d1 = __funnelshift_r(w[1], w[2], sh),
-                                   d2 = __funnelshift_r(w[2], w[3], sh), d3 = __funnelshift_r(w[3], w[4], sh);
+                    const uint32_t d0 = shf_r(w[0], w[1], sh), d1 = shf_r(w[1], w[2], sh),
+                                   d2 = shf_r(w[2], w[3], sh), d3 = shf_r(w[3], w[4], sh);
                     const uint32_t type = d0 & 0xffu, len = d0 >> 8;
                     crc = d1;
                     bad = (done + lane == 0 && type != 0xff);                // :20-21

@@ -64,7 +64,7 @@ __device__ __forceinline__ void stage_fragment(const uint8_t* __restrict__ src, 
         for (uint32_t j = lane; (j << 2) < len; j += 32) {
             const uint32_t a0 = __ldg(w + j);
             const uint32_t a1 = (r && (j << 2) + 4u - r < len) ? __ldg(w + j + 1) : 0u;
-            s32[j] = __funnelshift_r(a0, a1, sh);
+            s32[j] = shf_r(a0, a1, sh);
         }
         __syncwarp();                                        // the last word may spill into the padding zeroed below
     }

@@ -51,7 +51,9 @@ struct Entry { uint32_t tag, g0, g1, g2; };    // tag = position | epoch << 16; 
 
 SB_HD uint32_t fsr(uint32_t lo, uint32_t hi, uint32_t sh) {   // (hi:lo) >> sh, sh in {0,8,16,24}
 #ifdef __CUDA_ARCH__
-    return __funnelshift_r(lo, hi, sh);
+    uint32_t r_;
+    asm("shf.r.wrap.b32 %0, %1, %2, %3;" : "=r"(r_) : "r"(lo), "r"(hi), "r"(sh));   // not volatile: see snappy_device.cuh
+    return r_;
 #else
     return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
 #endif

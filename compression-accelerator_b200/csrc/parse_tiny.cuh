@@ -45,7 +45,9 @@ SB_THD uint32_t entries_for(uint32_t len) {                     // snappy.cc:445
 }
 SB_THD uint32_t fsr(uint32_t lo, uint32_t hi, uint32_t sh) {
 #ifdef __CUDA_ARCH__
-    return __funnelshift_r(lo, hi, sh);
+    uint32_t r_;
+    asm("shf.r.wrap.b32 %0, %1, %2, %3;" : "=r"(r_) : "r"(lo), "r"(hi), "r"(sh));   // not volatile: see snappy_device.cuh
+    return r_;
 #else
     return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
 #endif

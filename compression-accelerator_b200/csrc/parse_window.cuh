@@ -29,15 +29,15 @@ __device__ __forceinline__ void lds16u(const uint8_t* s, uint32_t pos, uint32_t&
     const uint32_t* w = reinterpret_cast<const uint32_t*>(s) + (pos >> 2);
     const uint32_t sh = (pos & 3u) << 3;
     uint32_t a0 = w[0], a1 = w[1], a2 = w[2], a3 = w[3], a4 = w[4];
-    b0 = __funnelshift_r(a0, a1, sh);
-    b1 = __funnelshift_r(a1, a2, sh);
-    b2 = __funnelshift_r(a2, a3, sh);
-    b3 = __funnelshift_r(a3, a4, sh);
+    b0 = shf_r(a0, a1, sh);
+    b1 = shf_r(a1, a2, sh);
+    b2 = shf_r(a2, a3, sh);
+    b3 = shf_r(a3, a4, sh);
 }
 
 // one SHF each: the funnel shift clamps the count at 32
-__device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return __funnelshift_lc(0u, kFull, s); }
-__device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return __funnelshift_lc(kFull, 0u, e); }
+__device__ __forceinline__ uint32_t lanes_from(uint32_t s) { return shf_lc(0u, kFull, s); }
+__device__ __forceinline__ uint32_t lanes_below(uint32_t e) { return shf_lc(kFull, 0u, e); }
 
 // ---- input accessors ------------------------------------------------------------------------
 struct SmemSrc {                         // fragment staged in shared memory (4-byte aligned, padded)
@@ -71,7 +71,7 @@ struct GlobalSrc {                       // fragment read in place from global m
         const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
         const uint32_t sh = ((uint32_t)a & 3u) << 3;
         const uint32_t a0 = __ldg(w), a1 = sh ? __ldg(w + 1) : 0u;
-        return __funnelshift_r(a0, a1, sh);
+        return shf_r(a0, a1, sh);
     }
     // as ld32, but never touches a word that lies entirely at or beyond position `end` (the
     // last fragment may end on the last mapped byte of the caller's buffer)
@@ -80,7 +80,7 @@ struct GlobalSrc {                       // fragment read in place from global m
         const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
         const uint32_t r = (uint32_t)a & 3u;
         const uint32_t a0 = __ldg(w), a1 = (r && pos + 4 - r < end) ? __ldg(w + 1) : 0u;
-        return __funnelshift_r(a0, a1, r << 3);
+        return shf_r(a0, a1, r << 3);
     }
     __device__ __forceinline__ void ld16(uint32_t pos, uint32_t& b0, uint32_t& b1, uint32_t& b2,
                                          uint32_t& b3) const {
@@ -89,10 +89,10 @@ struct GlobalSrc {                       // fragment read in place from global m
         const uint32_t sh = ((uint32_t)a & 3u) << 3;
         const uint32_t a0 = __ldg(w), a1 = __ldg(w + 1), a2 = __ldg(w + 2), a3 = __ldg(w + 3);
         const uint32_t a4 = sh ? __ldg(w + 4) : 0u;         // never touch a word without needed bytes
-        b0 = __funnelshift_r(a0, a1, sh);
-        b1 = __funnelshift_r(a1, a2, sh);
-        b2 = __funnelshift_r(a2, a3, sh);
-        b3 = __funnelshift_r(a3, a4, sh);
+        b0 = shf_r(a0, a1, sh);
+        b1 = shf_r(a1, a2, sh);
+        b2 = shf_r(a2, a3, sh);
+        b3 = shf_r(a3, a4, sh);
     }
 };
 

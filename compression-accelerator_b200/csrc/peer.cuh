@@ -107,10 +107,10 @@ __device__ __forceinline__ void peer_tile_copy(uint8_t* __restrict__ d, const ui
                 const uint32_t j = j0 + u * nthreads;
                 if (j < body) {
                     uint4 v;
-                    v.x = __funnelshift_r(a[u][0], a[u][1], sh);
-                    v.y = __funnelshift_r(a[u][1], a[u][2], sh);
-                    v.z = __funnelshift_r(a[u][2], a[u][3], sh);
-                    v.w = __funnelshift_r(a[u][3], a[u][4], sh);
+                    v.x = shf_r(a[u][0], a[u][1], sh);
+                    v.y = shf_r(a[u][1], a[u][2], sh);
+                    v.z = shf_r(a[u][2], a[u][3], sh);
+                    v.w = shf_r(a[u][3], a[u][4], sh);
                     d4[j] = v;
                 }
             }

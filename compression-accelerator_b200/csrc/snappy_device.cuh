@@ -15,6 +15,21 @@ constexpr uint32_t kMargin = 15;        // tests/snappy/snappy.cc:556 kInputMarg
 constexpr uint32_t kHashMul = 0x1e35a7bdu;  // tests/snappy/snappy.cc:92 (same constant as HashTable.scala:23)
 constexpr uint32_t kFull = 0xffffffffu;
 
+// Funnel shifts as plain (not volatile) asm.  The toolkit's __funnelshift_* are `asm volatile`: never removed when
+// their result is unused, never merged when repeated, and kept in program order with every other volatile asm --
+// all of which costs issue slots and scheduling freedom in the one-warp parsers (7 % of the page parser's
+// instructions were funnel shifts).
+__device__ __forceinline__ uint32_t shf_r(uint32_t lo, uint32_t hi, uint32_t s) {      // (hi:lo >> (s & 31)), low word
+    uint32_t r;
+    asm("shf.r.wrap.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(s));
+    return r;
+}
+__device__ __forceinline__ uint32_t shf_lc(uint32_t lo, uint32_t hi, uint32_t s) {     // (hi:lo << min(s, 32)), high word
+    uint32_t r;
+    asm("shf.l.clamp.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(s));
+    return r;
+}
+
 // tests/snappy/snappy.cc:445-456 CalculateTableSize: 256 <= next_pow2(len) <= 16384
 __host__ __device__ inline uint32_t table_entries(uint32_t len) {
     if (len > kMaxTable) return kMaxTable;
@@ -42,7 +57,7 @@ __host__ __device__ inline uint32_t put_varint32(uint8_t* dst, uint32_t v) {
 __device__ __forceinline__ uint32_t lds32u(const uint8_t* s, uint32_t pos) {
     const uint32_t* w = reinterpret_cast<const uint32_t*>(s);
     uint32_t i = pos >> 2;
-    return __funnelshift_r(w[i], w[i + 1], (pos & 3u) << 3);
+    return shf_r(w[i], w[i + 1], (pos & 3u) << 3);
 }
 
 __device__ __forceinline__ uint32_t hash32(uint32_t w, int shift) {  // snappy.cc:91-97
@@ -190,10 +205,10 @@ __device__ __forceinline__ uint32_t warp_emit_literal(uint8_t* out, uint32_t op,
         uint32_t sh = (q & 3u) << 3;
         uint32_t a0 = w[0], a1 = w[1], a2 = w[2], a3 = w[3], a4 = w[4];
         uint4 v;
-        v.x = __funnelshift_r(a0, a1, sh);
-        v.y = __funnelshift_r(a1, a2, sh);
-        v.z = __funnelshift_r(a2, a3, sh);
-        v.w = __funnelshift_r(a3, a4, sh);
+        v.x = shf_r(a0, a1, sh);
+        v.y = shf_r(a1, a2, sh);
+        v.z = shf_r(a2, a3, sh);
+        v.w = shf_r(a3, a4, sh);
         d4[j] = v;
     }
     uint32_t done = head + (body << 4);
