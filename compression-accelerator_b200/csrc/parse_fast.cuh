@@ -246,6 +246,12 @@ __device__ __forceinline__ void fast_evaluate(const uint8_t* s, uint32_t len, co
     FSTAT_ADD(2, lane);
     const uint32_t pos = (w << 5) + lane;
     uint32_t c = cring[((w & (kCandRing - 1)) << 5) + lane];
+    // A window that lies wholly inside a copy is marked by the chaser without its record, so the table warp may
+    // already have reused this ring slot for window w + 64 when its evaluator gets here: the candidates are then
+    // positions AHEAD of the window.  Nothing of such a window is emitted, but on periodic input a candidate from
+    // the future matches for kilobytes and the extension would read past the staged fragment (found by
+    // scripts/fuzz_decode.py: period 64 / 128 / 256, a full 64 KiB fragment).  A real candidate is always earlier.
+    if (c >= pos) c = kNoCand;
     uint32_t m = 0;
     uint32_t d0, d1, d2, d3, c0, c1, c2, c3;
     lds16u(s, pos, d0, d1, d2, d3);

@@ -22,6 +22,12 @@ def inputs():
     for seed, n in enumerate([1, 3, 4, 5, 31, 32, 33, 100, 4096, 65535, 65536, 65537, 200000]):
         yield "struct%d" % n, corpus.structured_random(n, 100 + seed)
     yield "empty", b""
+    # purely periodic data, period a multiple of the 32-position window: every copy is 1,024 bytes long and the
+    # windows inside it are marked without being evaluated first -- their evaluators may then find candidates of a
+    # LATER window in the ring (an out-of-range read in a full 64 KiB fragment before the fix; scripts/fuzz_decode.py)
+    for per, n in ((32, 65536), (64, 65536), (128, 190589), (256, 131072), (96, 65536), (60, 65536)):
+        base = bytes(np.random.default_rng(per).integers(0, 256, size=per, dtype=np.uint8))
+        yield "periodic%d_%d" % (per, n), (base * (n // per + 2))[:n]
 
 
 @pytest.mark.parametrize("name,data", list(inputs()), ids=[n for n, _ in inputs()])
