@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Differential run on the GPU: random inputs through every exact engine and the batch entry, every stream compared
-byte for byte with the CPU checker (compiled reference Snappy when present, else the port).
+"""Differential run on the GPU: random inputs through every exact engine, the fast mode and the batch entry, every
+stream compared byte for byte with the CPU checker (compiled reference Snappy when present, else the port; the fast
+mode against its sequential model, oracle/snappy_port.c port_fast_compress).
 
     python scripts/fuzz_parity.py [--seconds 120] [--seed 1]
 
@@ -39,7 +40,7 @@ def make_input(rng, n, corpus, text):
             out += seed_bytes[:int(rng.integers(4, 64))]
         return bytes(out[:n])
     if kind == 4:                                   # periodic with a random period and noise
-        per = int(rng.integers(1, 300))
+        per = int(rng.integers(1, 300)) if rng.integers(0, 3) else int(rng.choice([32, 64, 96, 128, 256, 512, 1024, 2048, 4096]))
         base = bytes(rng.integers(0, 256, size=per, dtype=np.uint8))
         arr = np.frombuffer((base * (n // per + 2))[:n], dtype=np.uint8).copy()
         for _ in range(int(rng.integers(0, 8))):
@@ -66,13 +67,14 @@ def main():
     rng = np.random.default_rng(a.seed)
     t0 = time.time()
     runs = fails = 0
-    modes = ["exact", "exact_lane", "exact_pipe", "exact_gtab"]
+    port = oracle_lib.port()
+    modes = ["exact", "exact_lane", "exact_pipe", "exact_gtab", "fast", "fast"]      # fast: against its sequential model
     while time.time() - t0 < a.seconds:
         if rng.integers(0, 3) < 2:                  # one stream, one engine
             n = int(rng.choice([int(rng.integers(1, 300)), int(rng.integers(300, 70000)), int(rng.integers(70000, 400000))]))
             data = make_input(rng, n, corpus, text)
             mode = modes[int(rng.integers(0, len(modes)))]
-            want = chk.compress(data)
+            want = port.fast_compress(data) if mode == "fast" else chk.compress(data)
             src = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
             dst, out_n = ctx.compress_device(src, mode=mode)
             ctx.sync()
@@ -88,14 +90,15 @@ def main():
             stride = length + int(rng.integers(0, 9))
             blob = make_input(rng, stride * count, corpus, text)
             src = torch.frombuffer(bytearray(blob), dtype=torch.uint8).cuda()
-            mode = "exact" if rng.integers(0, 4) else "exact_gtab"
+            mode = ["exact", "exact", "exact_gtab", "fast"][int(rng.integers(0, 4))]
             dst, ostride, sizes = ctx.compress_batch_device(src, length, stride, count, mode=mode)
             ctx.sync()
             out = dst.cpu().numpy()
             sz = sizes.cpu().numpy()
             runs += 1
             for i in (range(count) if count <= 200 else range(0, count, 9)):
-                want = chk.compress(blob[i * stride:i * stride + length])
+                one = blob[i * stride:i * stride + length]
+                want = port.fast_compress(one) if mode == "fast" else chk.compress(one)
                 if bytes(out[i * ostride:i * ostride + sz[i]]) != want:
                     fails += 1
                     print("MISMATCH batch mode=%s length=%d stride=%d count=%d i=%d seed=%d run=%d" % (
