@@ -69,7 +69,22 @@ def main():
     runs = fails = 0
     port = oracle_lib.port()
     modes = ["exact", "exact_lane", "exact_pipe", "exact_gtab", "fast", "fast"]      # fast: against its sequential model
+    L = pkg.lib()
+    na_dst = torch.zeros(pkg.max_compressed_length(1 << 20) + 64, dtype=torch.uint8, device="cuda")
+    na_n = torch.zeros(1, dtype=torch.int64, device="cuda")
     while time.time() - t0 < a.seconds:
+        if rng.integers(0, 8) == 0:                 # the no-allocation entry (inputs up to 1 MiB, its own scratch)
+            n = int(rng.choice([int(rng.integers(0, 300)), int(rng.integers(300, 70000)), int(rng.integers(70000, (1 << 20) + 1))]))
+            data = make_input(rng, n, corpus, text) if n else b""
+            src = torch.frombuffer(bytearray(data) if n else bytearray(1), dtype=torch.uint8).cuda()
+            torch.cuda.synchronize()
+            st = L.snappy_b200_compress_device_noalloc(src.data_ptr(), n, na_dst.data_ptr(), na_dst.numel(), na_n.data_ptr(), None)
+            torch.cuda.synchronize()
+            runs += 1
+            if st != 0 or bytes(na_dst[:int(na_n.item())].cpu().numpy()) != chk.compress(data):
+                fails += 1
+                print("MISMATCH noalloc n=%d status=%d seed=%d run=%d" % (n, st, a.seed, runs), flush=True)
+            continue
         if rng.integers(0, 3) < 2:                  # one stream, one engine
             n = int(rng.choice([int(rng.integers(1, 300)), int(rng.integers(300, 70000)), int(rng.integers(70000, 400000))]))
             data = make_input(rng, n, corpus, text)
