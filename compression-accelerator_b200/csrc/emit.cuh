@@ -188,9 +188,14 @@ struct SparseWalk {                      // per-lane view of 32 slots
 };
 
 // before = end of the last copy in front of my slot (carry for lanes with no non-empty lane below)
-__device__ __forceinline__ void sparse_load(const uint32_t* __restrict__ q, uint32_t i, uint32_t n,
+__device__ __forceinline__ uint32_t sparse_fetch(const uint32_t* __restrict__ q, uint32_t i, uint32_t n) {
+    return i < n ? __ldg(q + i) : 0u;
+}
+// `v` = slot i, fetched one round ahead by the walks below (a round's slots are an L2 / DRAM round trip that
+// nothing else in the round can hide)
+__device__ __forceinline__ void sparse_load(uint32_t v, uint32_t i,
                                             uint32_t carry, uint32_t lane, SparseWalk& k, uint32_t& nonempty) {
-    k.v = i < n ? __ldg(q + i) : 0u;
+    k.v = v;
     k.pos = sparse_pos(i, k.v); k.clen = sparse_len(k.v); k.off = sparse_off(k.v);
     k.end = k.v ? k.pos + k.clen : 0u;
     nonempty = __ballot_sync(kFull, k.v != 0u);
@@ -211,10 +216,14 @@ __device__ __forceinline__ void sparse_summary(const uint32_t* __restrict__ q, u
                                                uint32_t& last_end, uint32_t& bytes) {
     first_pos = kNoPos; last_end = kNoPos;
     uint32_t sum = 0, carry = 0;
+    const uint32_t lim = min(n, hi);
+    uint32_t v_next = sparse_fetch(q, lo + lane, lim);
     for (uint32_t base = lo; base < hi; base += 32) {
         SparseWalk k;
         uint32_t nonempty;
-        sparse_load(q, base + lane, min(n, hi), carry, lane, k, nonempty);
+        const uint32_t v = v_next;
+        v_next = sparse_fetch(q, base + 32 + lane, lim);
+        sparse_load(v, base + lane, carry, lane, k, nonempty);
         if (!nonempty) continue;
         const uint32_t fl = __ffs(nonempty) - 1, ll = 31 - __clz(nonempty);
         const bool seg_first = first_pos == kNoPos && lane == fl;      // its literal is added by the chain
@@ -302,10 +311,14 @@ __global__ void __launch_bounds__(kEmitThreads) emit_sparse_kernel(JobParams p) 
     __syncthreads();
     // second walk, now with the true carries: write the elements
     uint32_t carry = c.end_in[wid], op0 = c.out_in[wid];
+    const uint32_t lim = min(n, hi);
+    uint32_t v_next = sparse_fetch(q, lo + lane, lim);
     for (uint32_t base = lo; base < hi; base += 32) {
         SparseWalk k;
         uint32_t nonempty;
-        sparse_load(q, base + lane, min(n, hi), carry, lane, k, nonempty);
+        const uint32_t v = v_next;
+        v_next = sparse_fetch(q, base + 32 + lane, lim);
+        sparse_load(v, base + lane, carry, lane, k, nonempty);
         if (!nonempty) continue;
         k.lit = (k.v && k.pos > k.before) ? k.pos - k.before : 0u;
         const uint32_t lh = k.lit ? literal_header_size(k.lit) : 0u;
