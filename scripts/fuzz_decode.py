@@ -58,10 +58,9 @@ def main():
         if a.verbose:
             print("run %d: uncompress how=%d stream=%d B" % (runs, how, len(blob)), flush=True)
         try:                                                       # what the reference says
-            want_n = chk.uncompressed_length(blob) if hasattr(chk, "uncompressed_length") else None
-            if want_n is not None and want_n > (64 << 20):
+            if chk.uncompressed_length(blob) > (64 << 20):
                 continue                                           # a mutated preamble asking for gigabytes: skipped
-            want = chk.uncompress(blob, len(data) + 64) if want_n is None else chk.uncompress(blob)
+            want = chk.uncompress(blob)
         except ValueError:
             want = None
         try:

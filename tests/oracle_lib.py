@@ -92,7 +92,21 @@ class Port(_Lib):
         n = self.lib.port_fast_compress(data, len(data), out)
         return out.raw[:n]
 
-    def uncompress(self, data: bytes, cap: int) -> bytes:
+    def uncompressed_length(self, data: bytes) -> int:
+        """The varint32 preamble (snappy.cc:864-, GetUncompressedLength); ValueError when malformed."""
+        v = shift = 0
+        for i, b in enumerate(data[:5]):
+            if shift == 28 and (b & 0x7f) > 15:
+                break
+            v |= (b & 0x7f) << shift
+            if b < 128:
+                return v
+            shift += 7
+        raise ValueError("bad header")
+
+    def uncompress(self, data: bytes, cap: int = None) -> bytes:
+        if cap is None:
+            cap = self.uncompressed_length(data)
         out = C.create_string_buffer(cap + 16)
         n = C.c_size_t(0)
         rc = self.lib.port_uncompress(data, len(data), out, cap, C.byref(n))
